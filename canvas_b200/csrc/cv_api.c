@@ -1,0 +1,644 @@
+/*
+ * canvas_b200/csrc/cv_api.c -- host side of the pixel operations of include/canvas_b200.h:
+ * window arithmetic, short-circuits and the translation of a frame program (cv_frame_job)
+ * into the pre-digested DevJob the kernels consume.  Plain C; no pixel is touched on the CPU.
+ *
+ * Window rules follow /root/reference/src/cprocess/video_mix.c (copy :27-44, :73-105, cross
+ * :107-235 with the pull short-circuits :46-71, over :237-370), workspace.c:494-550 and
+ * video_reconstruct.c:69-76, with the INTENDED semantics where the reference's 9-region walk
+ * is buggy (min.x compared with min.y at video_mix.c:137,265; stale pixels for disjoint windows
+ * :161-169): inside the union box, a pixel covered by nobody is zero.
+ */
+#include "cv_internal.h"
+
+#include <stdlib.h>
+#include <string.h>
+
+/* ------------------------------------------------------------ box helpers */
+
+static DevBox to_dev( const box2i *b ) {
+    DevBox d = { b->min.x, b->min.y, b->max.x, b->max.y };
+    return d;
+}
+static box2i from_dev( const DevBox *d ) {
+    box2i b;
+    box2i_set( &b, d->x0, d->y0, d->x1, d->y1 );
+    return b;
+}
+static int dev_empty( const DevBox *b ) { return b->x1 < b->x0 || b->y1 < b->y0; }
+static DevBox dev_empty_box( void ) { DevBox d = { 0, 0, -1, -1 }; return d; }
+static DevBox dev_intersect( const DevBox *a, const DevBox *b ) {
+    DevBox d = { max( a->x0, b->x0 ), max( a->y0, b->y0 ), min( a->x1, b->x1 ), min( a->y1, b->y1 ) };
+    if( dev_empty( &d ) ) d = dev_empty_box();
+    return d;
+}
+static DevBox dev_union( const DevBox *a, const DevBox *b ) {
+    if( dev_empty( a ) ) return *b;
+    if( dev_empty( b ) ) return *a;
+    DevBox d = { min( a->x0, b->x0 ), min( a->y0, b->y0 ), max( a->x1, b->x1 ), max( a->y1, b->y1 ) };
+    return d;
+}
+static int box_width( const box2i *b ) { return b->max.x < b->min.x ? 0 : b->max.x - b->min.x + 1; }
+static int same_window( const box2i *a, const box2i *b ) {
+    return a->min.x == b->min.x && a->min.y == b->min.y && a->max.x == b->max.x && a->max.y == b->max.y;
+}
+
+/* ------------------------------------------------------------- job builder */
+
+typedef struct BuildOptions {
+    int pull_short_circuit;     /* crossfade: mix 0 / 1 fetch one source only (video_mix.c:50-55) */
+    float single_alpha;         /* alpha scale when the bottom is one source (copy_frame_alpha) */
+} BuildOptions;
+
+static int fill_source( DevSrc *d, const cv_source *s, const DevBox *full ) {
+    memset( d, 0, sizeof(*d) );
+    d->kind = s->kind;
+    d->cw = dev_empty_box();
+
+    switch( s->kind ) {
+        case CV_SRC_NONE:
+            return CV_OK;
+
+        case CV_SRC_F16: {
+            DevBox cw = to_dev( &s->f16.current_window );
+            d->cw = dev_intersect( &cw, full );
+            d->data = s->f16.data;
+            d->pitch = box_width( &s->f16.full_window );
+            d->ox = s->f16.full_window.min.x;
+            d->oy = s->f16.full_window.min.y;
+            if( !dev_empty( &d->cw ) && (!d->data || ((uintptr_t) d->data & 7)) )
+                return cvi_fail( CV_ERR_ARGUMENT, "f16 source: data is NULL or not 8-byte aligned" );
+            return CV_OK;
+        }
+
+        case CV_SRC_F32: {
+            DevBox cw = to_dev( &s->f32.current_window );
+            d->cw = dev_intersect( &cw, full );
+            d->data = s->f32.data;
+            d->pitch = box_width( &s->f32.full_window );
+            d->ox = s->f32.full_window.min.x;
+            d->oy = s->f32.full_window.min.y;
+            if( !dev_empty( &d->cw ) && (!d->data || ((uintptr_t) d->data & 15)) )
+                return cvi_fail( CV_ERR_ARGUMENT, "f32 source: data is NULL or not 16-byte aligned" );
+            return CV_OK;
+        }
+
+        case CV_SRC_CODED: {
+            const cv_coded *c = &s->coded;
+            if( c->sub_x != 1 && c->sub_x != 2 && c->sub_x != 4 )
+                return cvi_fail( CV_ERR_UNSUPPORTED, "coded source: sub_x %d (1, 2 or 4 supported)", c->sub_x );
+            if( c->matrix != CV_MATRIX_709 && c->matrix != CV_MATRIX_601 )
+                return cvi_fail( CV_ERR_UNSUPPORTED, "coded source: unknown matrix %d", c->matrix );
+            if( c->width <= 0 || c->height <= 0 || !c->plane[0] )
+                return cvi_fail( CV_ERR_ARGUMENT, "coded source: empty picture" );
+
+            if( c->layout == CV_LAYOUT_PLANAR ) {
+                if( !c->plane[1] || !c->plane[2] )
+                    return cvi_fail( CV_ERR_ARGUMENT, "coded source: planar layout needs three planes" );
+            }
+            else if( c->layout == CV_LAYOUT_UYVY || c->layout == CV_LAYOUT_YUY2 ) {
+                if( c->sub_x != 2 )
+                    return cvi_fail( CV_ERR_UNSUPPORTED, "coded source: packed layouts are 4:2:2 (sub_x 2)" );
+                if( ((uintptr_t) c->plane[0] & 3) || (c->stride[0] & 3) )
+                    return cvi_fail( CV_ERR_ARGUMENT, "coded source: packed rows must be 4-byte aligned" );
+            }
+            else
+                return cvi_fail( CV_ERR_UNSUPPORTED, "coded source: unknown layout %d", c->layout );
+
+            /* video_reconstruct.c:69-76 */
+            DevBox pic = { c->pic_x, c->pic_y, c->pic_x + c->width - 1, c->pic_y + c->height - 1 };
+            d->cw = dev_intersect( &pic, full );
+            for( int i = 0; i < 3; i++ ) { d->plane[i] = c->plane[i]; d->stride[i] = c->stride[i]; }
+            d->layout = c->layout; d->width = c->width; d->height = c->height;
+            d->sub_shift = c->sub_x == 4 ? 2 : (c->sub_x == 2 ? 1 : 0);
+            d->matrix = c->matrix; d->pic_x = c->pic_x; d->pic_y = c->pic_y;
+            d->last_chroma = (c->width - 1) / c->sub_x;
+            return CV_OK;
+        }
+    }
+    return cvi_fail( CV_ERR_ARGUMENT, "unknown source kind %d", s->kind );
+}
+
+static int f16_pair_ok( const void *data, int pitch, int ox, int full_x ) {
+    return ((uintptr_t) data & 15) == 0 && (pitch & 1) == 0 && (((int64_t) ox - full_x) & 1) == 0;
+}
+
+/*
+ * Fills `dj` from `job`; returns the kernel shape in *shape and the pixels per item in *px.
+ * dj->total_items == 0 means "nothing to launch" (empty result).  Writes the result window into
+ * job->current_window and the output frame structs.
+ */
+static int build_job( cv_frame_job *job, const BuildOptions *opt, DevJob *dj, int *shape, int *px ) {
+    memset( dj, 0, sizeof(*dj) );
+
+    box2i full;
+    if( job->out ) full = job->out->full_window;
+    else if( job->out_f32 ) full = job->out_f32->full_window;
+    else full = job->full_window;
+
+    if( job->out && job->out_f32 && !same_window( &job->out->full_window, &job->out_f32->full_window ) )
+        return cvi_fail( CV_ERR_ARGUMENT, "frame job: out and out_f32 must share full_window" );
+    if( job->out_u8 && !job->u8_table )
+        return cvi_fail( CV_ERR_ARGUMENT, "frame job: out_u8 needs u8_table" );
+    if( job->layer_count < 0 || job->layer_count > CV_MAX_LAYERS )
+        return cvi_fail( CV_ERR_ARGUMENT, "frame job: layer_count %d (0..%d)", job->layer_count, CV_MAX_LAYERS );
+
+    box2i_set_empty( &job->current_window );
+    if( job->out ) box2i_set_empty( &job->out->current_window );
+    if( job->out_f32 ) box2i_set_empty( &job->out_f32->current_window );
+
+    const DevBox dfull = to_dev( &full );
+    if( dev_empty( &dfull ) )
+        return CV_OK;
+
+    dj->full_x = full.min.x;
+    dj->full_y = full.min.y;
+    dj->out_pitch = box_width( &full );
+    dj->out16 = job->out ? job->out->data : NULL;
+    dj->out32 = job->out_f32 ? job->out_f32->data : NULL;
+    dj->out8 = job->out_u8;
+    dj->u8tab = job->u8_table;
+    dj->single_alpha = 1.0f;
+
+    if( (job->out && !dj->out16) || (job->out_f32 && !dj->out32) )
+        return cvi_fail( CV_ERR_ARGUMENT, "frame job: output frame without data" );
+    if( ((uintptr_t) dj->out16 & 7) || ((uintptr_t) dj->out32 & 15) || ((uintptr_t) dj->out8 & 3) )
+        return cvi_fail( CV_ERR_ARGUMENT, "frame job: misaligned output pointer" );
+
+    /* ---- bottom ---- */
+    int rc;
+    DevSrc sa, sb;
+    if( (rc = fill_source( &sa, &job->a, &dfull )) ) return rc;
+    if( (rc = fill_source( &sb, &job->b, &dfull )) ) return rc;
+
+    DevBox under = dev_empty_box();
+    dj->bottom_mode = DEV_BOTTOM_NONE;
+
+    if( sa.kind != CV_SRC_NONE && sb.kind != CV_SRC_NONE ) {
+        const float mix_b = clampf( job->mix_b, 0.0f, 1.0f );
+        const float mix_a = 1.0f - mix_b;
+
+        if( opt->pull_short_circuit && mix_b == 0.0f ) {
+            dj->a = sa; dj->bottom_mode = DEV_BOTTOM_SINGLE;
+        }
+        else if( opt->pull_short_circuit && mix_b == 1.0f ) {
+            dj->a = sb; dj->bottom_mode = DEV_BOTTOM_SINGLE;
+        }
+        else if( dev_empty( &sa.cw ) ) {         /* video_mix.c:111-114 -> copy_frame_alpha(b, mix_b) */
+            dj->a = sb; dj->bottom_mode = DEV_BOTTOM_SINGLE; dj->single_alpha = mix_b;
+        }
+        else if( dev_empty( &sb.cw ) ) {         /* video_mix.c:115-118 */
+            dj->a = sa; dj->bottom_mode = DEV_BOTTOM_SINGLE; dj->single_alpha = mix_a;
+        }
+        else {
+            dj->a = sa; dj->b = sb; dj->bottom_mode = DEV_BOTTOM_CROSS;
+            dj->mix_a = mix_a; dj->mix_b = mix_b;
+            under = dev_union( &sa.cw, &sb.cw );
+        }
+    }
+    else if( sa.kind != CV_SRC_NONE || sb.kind != CV_SRC_NONE ) {
+        dj->a = (sa.kind != CV_SRC_NONE) ? sa : sb;
+        dj->bottom_mode = DEV_BOTTOM_SINGLE;
+        dj->single_alpha = clampf( opt->single_alpha, 0.0f, 1.0f );
+    }
+
+    if( dj->bottom_mode == DEV_BOTTOM_SINGLE ) {
+        /* video_copy_frame_alpha_f32: alpha 0 or an empty window leaves nothing (video_mix.c:80-93) */
+        if( dj->single_alpha == 0.0f || dev_empty( &dj->a.cw ) )
+            dj->bottom_mode = DEV_BOTTOM_NONE;
+        else
+            under = dj->a.cw;
+    }
+
+    int coded = 0;
+    if( dj->bottom_mode != DEV_BOTTOM_NONE )
+        coded = dj->a.kind == CV_SRC_CODED || (dj->bottom_mode == DEV_BOTTOM_CROSS && dj->b.kind == CV_SRC_CODED);
+
+    /* ---- layers (workspace.c:530-547 / video_mix.c:243-249) ---- */
+    int pair_ok = dj->out16 ? f16_pair_ok( dj->out16, dj->out_pitch, dj->full_x, dj->full_x ) : ((dj->out_pitch & 1) == 0);
+    int n = 0;
+
+    for( int i = 0; i < job->layer_count; i++ ) {
+        const cv_layer *L = &job->layers[i];
+        const float mix = clampf( L->mix, 0.0f, 1.0f );
+        DevBox cw = to_dev( &L->frame.current_window );
+        cw = dev_intersect( &cw, &dfull );
+
+        if( dev_empty( &cw ) || mix == 0.0f )
+            continue;
+        if( !L->frame.data || ((uintptr_t) L->frame.data & 7) )
+            return cvi_fail( CV_ERR_ARGUMENT, "layer %d: data is NULL or not 8-byte aligned", i );
+
+        DevLayer *d = &dj->layer[n++];
+        d->data = L->frame.data;
+        d->pitch = box_width( &L->frame.full_window );
+        d->ox = L->frame.full_window.min.x;
+        d->oy = L->frame.full_window.min.y;
+        d->mix = mix;
+        d->cw = cw;
+        d->under = under;
+        under = dev_union( &under, &cw );
+        pair_ok = pair_ok && f16_pair_ok( d->data, d->pitch, d->ox, dj->full_x );
+    }
+    dj->n_layers = n;
+
+    /* ---- result window and work decomposition ---- */
+    dj->region = under;
+    if( dev_empty( &under ) )
+        return CV_OK;
+
+    job->current_window = from_dev( &under );
+    if( job->out ) job->out->current_window = job->current_window;
+    if( job->out_f32 ) job->out_f32->current_window = job->current_window;
+
+    *px = pair_ok ? 2 : 1;
+    *shape = coded ? KB_CODED : (dj->bottom_mode != DEV_BOTTOM_NONE ? KB_GENERAL : KB_LAYERS);
+
+    if( *px == 2 ) {
+        dj->item_x0 = dj->full_x + ((under.x0 - dj->full_x) & ~1);
+        dj->items_per_row = (uint32_t)( (under.x1 - dj->item_x0) / 2 + 1 );
+    }
+    else {
+        dj->item_x0 = under.x0;
+        dj->items_per_row = (uint32_t)( under.x1 - under.x0 + 1 );
+    }
+    dj->rows = (uint32_t)( under.y1 - under.y0 + 1 );
+
+    const uint64_t total = (uint64_t) dj->items_per_row * dj->rows;
+    if( total > 0xFFFFFFFFu )
+        return cvi_fail( CV_ERR_UNSUPPORTED, "frame job: window too large" );
+    dj->total_items = (uint32_t) total;
+    dj->div_magic = cvi_div_magic( dj->items_per_row );
+    return CV_OK;
+}
+
+/* ------------------------------------------------------------ frame programs */
+
+static int render_jobs( cv_frame_job *jobs, int count, const BuildOptions *opt, cv_stream stream ) {
+    if( !cvi_device() ) {
+        for( int i = 0; i < count; i++ ) {
+            box2i_set_empty( &jobs[i].current_window );
+            if( jobs[i].out ) box2i_set_empty( &jobs[i].out->current_window );
+            if( jobs[i].out_f32 ) box2i_set_empty( &jobs[i].out_f32->current_window );
+        }
+        return CV_ERR_NOT_INITIALISED;
+    }
+    if( count <= 0 ) return CV_OK;
+    if( !jobs ) return cvi_fail( CV_ERR_ARGUMENT, "cv_render_frames: NULL jobs" );
+
+    cudaStream_t s = cvi_stream( stream );
+
+    if( count == 1 ) {
+        DevJob dj;
+        int shape = 0, px = 1;
+        int rc = build_job( &jobs[0], opt, &dj, &shape, &px );
+        if( rc || dj.total_items == 0 ) return rc;
+        return cvi_launch_jobs( shape, px, &dj, 1, s );
+    }
+
+    /* group by (shape, px): jobs are independent, so their order inside the stream is free */
+    DevJob *built = (DevJob *) malloc( sizeof(DevJob) * (size_t) count );
+    DevJob *group = (DevJob *) malloc( sizeof(DevJob) * (size_t) count );
+    int *key = (int *) malloc( sizeof(int) * (size_t) count );
+    if( !built || !group || !key ) {
+        free( built ); free( group ); free( key );
+        return cvi_fail( CV_ERR_MEMORY, "cv_render_frames: out of host memory" );
+    }
+
+    int rc = CV_OK;
+    for( int i = 0; i < count && !rc; i++ ) {
+        int shape = 0, px = 1;
+        rc = build_job( &jobs[i], opt, &built[i], &shape, &px );
+        key[i] = built[i].total_items ? shape * 2 + (px == 2) : -1;
+    }
+
+    for( int k = 0; k < KB_COUNT * 2 && !rc; k++ ) {
+        int n = 0;
+        for( int i = 0; i < count; i++ )
+            if( key[i] == k ) group[n++] = built[i];
+        if( n )
+            rc = cvi_launch_jobs( k / 2, (k & 1) ? 2 : 1, group, n, s );
+    }
+
+    free( built ); free( group ); free( key );
+    return rc;
+}
+
+int cv_render_frames( cv_frame_job *jobs, int count, cv_stream stream ) {
+    const BuildOptions opt = { 1, 1.0f };
+    return render_jobs( jobs, count, &opt, stream );
+}
+
+int cv_convert_ycbcr8( rgba_frame_f16 *frame, const cv_coded *image, cv_stream stream ) {
+    if( !frame || !image ) return cvi_fail( CV_ERR_ARGUMENT, "cv_convert_ycbcr8: NULL argument" );
+    cv_frame_job job;
+    memset( &job, 0, sizeof(job) );
+    job.a.kind = CV_SRC_CODED;
+    job.a.coded = *image;
+    job.out = frame;
+    return cv_render_frames( &job, 1, stream );
+}
+
+int cv_mix_cross_f16( rgba_frame_f16 *out, const rgba_frame_f16 *a, const rgba_frame_f16 *b, float mix_b, cv_stream stream ) {
+    if( !out || !a || !b ) return cvi_fail( CV_ERR_ARGUMENT, "cv_mix_cross_f16: NULL argument" );
+    cv_frame_job job;
+    memset( &job, 0, sizeof(job) );
+    job.a.kind = CV_SRC_F16; job.a.f16 = *a;
+    job.b.kind = CV_SRC_F16; job.b.f16 = *b;
+    job.mix_b = mix_b;
+    job.out = out;
+    return cv_render_frames( &job, 1, stream );
+}
+
+int cv_composite_over_f16( rgba_frame_f16 *out, const cv_layer *layers, int count, cv_stream stream ) {
+    if( !out || (count > 0 && !layers) ) return cvi_fail( CV_ERR_ARGUMENT, "cv_composite_over_f16: NULL argument" );
+    if( count < 0 ) return cvi_fail( CV_ERR_ARGUMENT, "cv_composite_over_f16: negative count" );
+
+    cv_frame_job job;
+    memset( &job, 0, sizeof(job) );
+
+    if( count <= CV_MAX_LAYERS ) {
+        job.layer_count = count;
+        if( count ) memcpy( job.layers, layers, sizeof(cv_layer) * (size_t) count );
+        job.out = out;
+        return cv_render_frames( &job, 1, stream );
+    }
+
+    /* deep stacks: CV_MAX_LAYERS at a time through a pooled f32 accumulator (no extra rounding) */
+    rgba_frame_f32 acc;
+    int rc = cv_frame_alloc_f32( &acc, &out->full_window, CV_MEM_DEVICE );
+    if( rc ) { box2i_set_empty( &out->current_window ); return rc; }
+
+    int done = 0;
+    while( done < count && !rc ) {
+        const int n = (count - done > CV_MAX_LAYERS) ? CV_MAX_LAYERS : count - done;
+        const int last = (done + n == count);
+        memset( &job, 0, sizeof(job) );
+        if( done ) { job.a.kind = CV_SRC_F32; job.a.f32 = acc; }
+        job.layer_count = n;
+        memcpy( job.layers, layers + done, sizeof(cv_layer) * (size_t) n );
+        if( last ) job.out = out; else job.out_f32 = &acc;
+        rc = cv_render_frames( &job, 1, stream );
+        done += n;
+    }
+
+    /* the accumulator goes back to the pool; later users are ordered behind us on `stream` only,
+     * so wait for the chain before another stream may pick the block up */
+    if( !rc ) rc = cv_stream_sync( stream );
+    cv_frame_free_f32( &acc, CV_MEM_DEVICE );
+    if( rc ) box2i_set_empty( &out->current_window );
+    return rc;
+}
+
+int cv_copy_frame_f16( rgba_frame_f16 *out, const rgba_frame_f16 *in, cv_stream stream ) {
+    if( !out || !in ) return cvi_fail( CV_ERR_ARGUMENT, "cv_copy_frame_f16: NULL argument" );
+    if( !cvi_device() ) { box2i_set_empty( &out->current_window ); return CV_ERR_NOT_INITIALISED; }
+
+    /* video_mix.c:27-44: a strided row copy, done by the copy engine (bit-preserving) */
+    box2i inner;
+    box2i_intersect( &inner, &out->full_window, &in->current_window );
+    out->current_window = inner;
+    if( box2i_is_empty( &inner ) ) {
+        box2i_set_empty( &out->current_window );
+        return CV_OK;
+    }
+
+    const size_t out_pitch = (size_t) box_width( &out->full_window ) * sizeof(rgba_f16);
+    const size_t in_pitch = (size_t) box_width( &in->full_window ) * sizeof(rgba_f16);
+    const rgba_f16 *src = in->data + (size_t)(inner.min.y - in->full_window.min.y) * box_width( &in->full_window ) + (inner.min.x - in->full_window.min.x);
+    rgba_f16 *dst = out->data + (size_t)(inner.min.y - out->full_window.min.y) * box_width( &out->full_window ) + (inner.min.x - out->full_window.min.x);
+
+    return cvi_cuda( cudaMemcpy2DAsync( dst, out_pitch, src, in_pitch, (size_t) box_width( &inner ) * sizeof(rgba_f16),
+        (size_t)(inner.max.y - inner.min.y + 1), cudaMemcpyDeviceToDevice, cvi_stream( stream ) ), "cudaMemcpy2DAsync(copy_frame)" );
+}
+
+/* ------------------------------------------------------------- f32 frame ops */
+
+int cv_copy_frame_alpha_f32( rgba_frame_f32 *out, const rgba_frame_f32 *in, float alpha, cv_stream stream ) {
+    if( !out || !in ) return cvi_fail( CV_ERR_ARGUMENT, "cv_copy_frame_alpha_f32: NULL argument" );
+    alpha = clampf( alpha, 0.0f, 1.0f );
+
+    if( out->data == in->data && alpha == 1.0f )      /* video_mix.c:76-78 */
+        return cvi_device() ? CV_OK : CV_ERR_NOT_INITIALISED;
+
+    cv_frame_job job;
+    memset( &job, 0, sizeof(job) );
+    job.a.kind = CV_SRC_F32; job.a.f32 = *in;
+    job.out_f32 = out;
+    const BuildOptions opt = { 0, alpha };
+    return render_jobs( &job, 1, &opt, stream );
+}
+
+int cv_mix_cross_f32( rgba_frame_f32 *out, const rgba_frame_f32 *a, const rgba_frame_f32 *b, float mix_b, cv_stream stream ) {
+    if( !out || !a || !b ) return cvi_fail( CV_ERR_ARGUMENT, "cv_mix_cross_f32: NULL argument" );
+    cv_frame_job job;
+    memset( &job, 0, sizeof(job) );
+    job.a.kind = CV_SRC_F32; job.a.f32 = *a;
+    job.b.kind = CV_SRC_F32; job.b.f32 = *b;
+    job.mix_b = mix_b;
+    job.out_f32 = out;
+    const BuildOptions opt = { 0, 1.0f };        /* video_mix_cross_f32 itself has no 0/1 short-circuit */
+    return render_jobs( &job, 1, &opt, stream );
+}
+
+int cv_mix_over_f32( rgba_frame_f32 *out, const rgba_frame_f32 *b, float mix_b, cv_stream stream ) {
+    if( !out || !b ) return cvi_fail( CV_ERR_ARGUMENT, "cv_mix_over_f32: NULL argument" );
+    if( !cvi_device() ) return CV_ERR_NOT_INITIALISED;
+    mix_b = clampf( mix_b, 0.0f, 1.0f );
+
+    if( box2i_is_empty( &out->current_window ) )          /* video_mix.c:243-246 */
+        return cv_copy_frame_alpha_f32( out, b, mix_b, stream );
+    if( box2i_is_empty( &b->current_window ) || mix_b == 0.0f )
+        return CV_OK;
+
+    const DevBox full = to_dev( &out->full_window );
+    DevBox ocw = to_dev( &out->current_window ), bcw = to_dev( &b->current_window );
+    ocw = dev_intersect( &ocw, &full );
+    bcw = dev_intersect( &bcw, &full );
+    const DevBox region = dev_union( &ocw, &bcw );
+    if( dev_empty( &region ) ) return CV_OK;
+
+    OverF32Args args;
+    memset( &args, 0, sizeof(args) );
+    args.out = (float4 *) out->data; args.b = (const float4 *) b->data;
+    args.out_pitch = box_width( &out->full_window ); args.out_ox = out->full_window.min.x; args.out_oy = out->full_window.min.y;
+    args.b_pitch = box_width( &b->full_window ); args.b_ox = b->full_window.min.x; args.b_oy = b->full_window.min.y;
+    args.out_cw = ocw; args.b_cw = bcw; args.region = region; args.mix = mix_b;
+    args.width = (uint32_t)( region.x1 - region.x0 + 1 );
+    args.total = args.width * (uint32_t)( region.y1 - region.y0 + 1 );
+    args.magic = cvi_div_magic( args.width );
+
+    out->current_window = from_dev( &region );
+    return cvi_launch_over_f32( &args, cvi_stream( stream ) );
+}
+
+int cv_frame_f16_to_f32( rgba_frame_f32 *out, const rgba_frame_f16 *in, cv_stream stream ) {
+    if( !out || !in ) return cvi_fail( CV_ERR_ARGUMENT, "cv_frame_f16_to_f32: NULL argument" );
+    cv_frame_job job;
+    memset( &job, 0, sizeof(job) );
+    job.a.kind = CV_SRC_F16; job.a.f16 = *in;
+    job.out_f32 = out;
+    return cv_render_frames( &job, 1, stream );
+}
+
+int cv_frame_f32_to_f16( rgba_frame_f16 *out, const rgba_frame_f32 *in, cv_stream stream ) {
+    if( !out || !in ) return cvi_fail( CV_ERR_ARGUMENT, "cv_frame_f32_to_f16: NULL argument" );
+    cv_frame_job job;
+    memset( &job, 0, sizeof(job) );
+    job.a.kind = CV_SRC_F32; job.a.f32 = *in;
+    job.out = out;
+    return cv_render_frames( &job, 1, stream );
+}
+
+/* --------------------------------------------------- half arrays and tables */
+
+int cv_half_from_float( half *out, const float *in, size_t count, cv_stream stream ) {
+    if( !cvi_device() ) return CV_ERR_NOT_INITIALISED;
+    if( count && (!out || !in) ) return cvi_fail( CV_ERR_ARGUMENT, "cv_half_from_float: NULL argument" );
+    return cvi_launch_half_from_float( out, in, count, cvi_stream( stream ) );
+}
+
+int cv_half_to_float( float *out, const half *in, size_t count, cv_stream stream ) {
+    if( !cvi_device() ) return CV_ERR_NOT_INITIALISED;
+    if( count && (!out || !in) ) return cvi_fail( CV_ERR_ARGUMENT, "cv_half_to_float: NULL argument" );
+    return cvi_launch_half_to_float( out, in, count, cvi_stream( stream ) );
+}
+
+int cv_half_lookup( const half *table, half *out, const half *in, size_t count, cv_stream stream ) {
+    if( !cvi_device() ) return CV_ERR_NOT_INITIALISED;
+    if( count && (!table || !out || !in) ) return cvi_fail( CV_ERR_ARGUMENT, "cv_half_lookup: NULL argument" );
+    return cvi_launch_lookup( table, out, in, count, cvi_stream( stream ) );
+}
+
+int cv_transfer( int which, half *out, const half *in, size_t count, cv_stream stream ) {
+    CvDevice *dev = cvi_device();
+    if( !dev ) return CV_ERR_NOT_INITIALISED;
+    if( which < 0 || which >= CV_LUT_COUNT ) return cvi_fail( CV_ERR_ARGUMENT, "cv_transfer: unknown table %d", which );
+    return cv_half_lookup( dev->lut[which], out, in, count, stream );
+}
+
+/* ------------------------------------------------------------ 8-bit encodes */
+
+int cv_upload_display_table( float rendering_intent, uint8_t **table ) {
+    CvDevice *dev = cvi_device();
+    if( !dev ) return CV_ERR_NOT_INITIALISED;
+    if( !table ) return cvi_fail( CV_ERR_ARGUMENT, "cv_upload_display_table: NULL result" );
+
+    uint8_t *ramp = (uint8_t *) malloc( HALF_COUNT ), *composed = (uint8_t *) malloc( HALF_COUNT );
+    if( !ramp || !composed ) { free( ramp ); free( composed ); return cvi_fail( CV_ERR_MEMORY, "out of host memory" ); }
+
+    /* widget_gl.c:297-306: sRGB transfer first, then the rendering-intent ramp */
+    cv_build_intent_ramp( rendering_intent, ramp );
+    const half *srgb = cv_host_lut( CV_LUT_LINEAR_TO_SRGB );
+    for( int i = 0; i < HALF_COUNT; i++ )
+        composed[i] = ramp[srgb[i]];
+
+    void *devptr = NULL;
+    int rc = cvi_pool_alloc( &devptr, HALF_COUNT );
+    if( !rc ) rc = cvi_cuda( cudaMemcpy( devptr, composed, HALF_COUNT, cudaMemcpyHostToDevice ), "cudaMemcpy(display table)" );
+    free( ramp ); free( composed );
+    *table = (uint8_t *) devptr;
+    return rc;
+}
+
+int cv_encode_u8( rgba_frame_f16 *frame, const uint8_t *u8_table, rgba_u8 *target, int write_back, cv_stream stream ) {
+    CvDevice *dev = cvi_device();
+    if( !dev ) return CV_ERR_NOT_INITIALISED;
+    if( !frame || !u8_table || !target ) return cvi_fail( CV_ERR_ARGUMENT, "cv_encode_u8: NULL argument" );
+
+    box2i win;
+    box2i_intersect( &win, &frame->current_window, &frame->full_window );
+    if( box2i_is_empty( &win ) ) return CV_OK;
+
+    if( !write_back ) {
+        /* one pass through the frame program: source = frame, output = u8 only */
+        cv_frame_job job;
+        memset( &job, 0, sizeof(job) );
+        job.a.kind = CV_SRC_F16; job.a.f16 = *frame;
+        job.out_u8 = target; job.u8_table = u8_table;
+        job.full_window = frame->full_window;
+        return cv_render_frames( &job, 1, stream );
+    }
+
+    /* with write-back the sRGB-encoded halves also replace the frame's pixels (widget_gl.c:297-299) */
+    EncodeArgs args;
+    memset( &args, 0, sizeof(args) );
+    args.frame = (uint2 *) frame->data; args.target = (uint32_t *) target;
+    args.srgb = dev->lut[CV_LUT_LINEAR_TO_SRGB]; args.ramp = u8_table;
+    args.pitch = box_width( &frame->full_window ); args.ox = frame->full_window.min.x; args.oy = frame->full_window.min.y;
+    args.win = to_dev( &win );
+    args.width = (uint32_t) box_width( &win );
+    args.total = args.width * (uint32_t)( win.max.y - win.min.y + 1 );
+    args.magic = cvi_div_magic( args.width );
+    args.write_back = 1;
+    return cvi_launch_encode_u8( &args, cvi_stream( stream ) );
+}
+
+int cv_to_argb32( const rgba_frame_f16 *frame, uint32_t *out, cv_stream stream ) {
+    CvDevice *dev = cvi_device();
+    if( !dev ) return CV_ERR_NOT_INITIALISED;
+    if( !frame || !out ) return cvi_fail( CV_ERR_ARGUMENT, "cv_to_argb32: NULL argument" );
+    if( box2i_is_empty( &frame->current_window ) ) return CV_OK;
+
+    ArgbArgs args;
+    memset( &args, 0, sizeof(args) );
+    args.frame = (const uint2 *) frame->data; args.out = out; args.ramp45 = dev->gamma45;
+    args.pitch = box_width( &frame->full_window ); args.ox = frame->full_window.min.x; args.oy = frame->full_window.min.y;
+    args.win = to_dev( &frame->current_window );
+    args.width = (uint32_t) box_width( &frame->current_window );
+    args.total = args.width * (uint32_t)( frame->current_window.max.y - frame->current_window.min.y + 1 );
+    args.magic = cvi_div_magic( args.width );
+    return cvi_launch_to_argb32( &args, cvi_stream( stream ) );
+}
+
+/* ------------------------------------------------------- RGB -> Y'CbCr 8-bit */
+
+int cv_subsample_ycbcr8( rgba_frame_f16 *frame, const cv_coded *image, cv_stream stream ) {
+    CvDevice *dev = cvi_device();
+    if( !dev ) return CV_ERR_NOT_INITIALISED;
+    if( !frame || !image ) return cvi_fail( CV_ERR_ARGUMENT, "cv_subsample_ycbcr8: NULL argument" );
+    if( image->sub_x != 1 && image->sub_x != 2 && image->sub_x != 4 )
+        return cvi_fail( CV_ERR_UNSUPPORTED, "cv_subsample_ycbcr8: sub_x %d", image->sub_x );
+    if( image->layout != CV_LAYOUT_PLANAR && image->sub_x != 2 )
+        return cvi_fail( CV_ERR_UNSUPPORTED, "cv_subsample_ycbcr8: packed layouts are 4:2:2" );
+    if( image->matrix != CV_MATRIX_709 && image->matrix != CV_MATRIX_601 )
+        return cvi_fail( CV_ERR_UNSUPPORTED, "cv_subsample_ycbcr8: unknown matrix" );
+
+    /* video_subsample.c:122-128 */
+    box2i pic, win;
+    box2i_set( &pic, image->pic_x, image->pic_y, image->pic_x + image->width - 1, image->pic_y + image->height - 1 );
+    box2i_intersect( &win, &pic, &frame->current_window );
+    if( box2i_is_empty( &win ) ) return CV_OK;
+
+    const int shift = image->sub_x == 4 ? 2 : (image->sub_x == 2 ? 1 : 0);
+
+    SubsampleArgs args;
+    memset( &args, 0, sizeof(args) );
+    args.frame = (uint2 *) frame->data;
+    args.pitch = box_width( &frame->full_window ); args.ox = frame->full_window.min.x; args.oy = frame->full_window.min.y;
+    for( int i = 0; i < 3; i++ ) { args.plane[i] = image->plane[i]; args.stride[i] = image->stride[i]; }
+    args.layout = image->layout; args.sub_shift = shift; args.matrix = image->matrix;
+    args.pic_x = image->pic_x; args.pic_y = image->pic_y;
+    args.wmin = win.min.x - image->pic_x; args.wmax = win.max.x - image->pic_x;
+    args.row0 = win.min.y - image->pic_y; args.rows = win.max.y - win.min.y + 1;
+    args.tx0 = args.wmin >> shift;
+    args.tx_count = (uint32_t)( (args.wmax >> shift) - args.tx0 + 1 );
+    args.total = args.tx_count * (uint32_t) args.rows;
+    args.magic = cvi_div_magic( args.tx_count );
+    args.lut = dev->lut[CV_LUT_LINEAR_TO_709];
+
+    int rc = cvi_launch_subsample( &args, cvi_stream( stream ) );
+    if( rc ) return rc;
+
+    /* :147 -- the table is applied in place to the window of the INPUT frame (second pass, so the
+     * first one never reads a pixel that was already transformed) */
+    LookupWindowArgs lw;
+    memset( &lw, 0, sizeof(lw) );
+    lw.frame = args.frame; lw.pitch = args.pitch; lw.ox = args.ox; lw.oy = args.oy;
+    lw.win = to_dev( &win );
+    lw.width = (uint32_t) box_width( &win );
+    lw.total = lw.width * (uint32_t) args.rows;
+    lw.magic = cvi_div_magic( lw.width );
+    lw.lut = args.lut;
+    return cvi_launch_lookup_window( &lw, cvi_stream( stream ) );
+}

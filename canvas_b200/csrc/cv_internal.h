@@ -1,0 +1,150 @@
+/*
+ * canvas_b200/csrc/cv_internal.h -- shared between the runtime, the host-side job
+ * builder and the kernels.  Not installed; the public surface is the headers under include/.
+ */
+#ifndef CV_INTERNAL_H
+#define CV_INTERNAL_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <pthread.h>
+#include "canvas_b200.h"
+
+#define CV_MAX_DEVICES 16
+
+/* ---- device-side job description (what one frame program needs, pre-digested) ---- */
+
+typedef struct DevBox { int32_t x0, y0, x1, y1; } DevBox;      /* inclusive, empty <=> x1 < x0 || y1 < y0 */
+
+typedef struct DevSrc {
+    int32_t kind;               /* CV_SRC_* */
+    int32_t pitch;              /* pixels per row of the f16/f32 frame */
+    int32_t ox, oy;             /* full_window.min of the f16/f32 frame */
+    const void *data;           /* f16 or f32 pixels */
+    DevBox cw;                  /* valid pixels, already clipped to the output's full_window */
+    /* CV_SRC_CODED */
+    const uint8_t *plane[3];
+    int32_t stride[3];
+    int32_t layout, width, height, sub_shift, matrix, pic_x, pic_y;
+    int32_t last_chroma;        /* (width - 1) / sub_x: the last chroma sample that exists */
+} DevSrc;
+
+typedef struct DevLayer {
+    const void *data;           /* f16 pixels */
+    int32_t pitch, ox, oy;
+    float mix;
+    DevBox cw;                  /* clipped to the output's full_window; never empty (empty layers are dropped) */
+    DevBox under;               /* box already defined below this layer (running union); may be empty */
+} DevLayer;
+
+enum { DEV_BOTTOM_NONE = 0, DEV_BOTTOM_SINGLE = 1, DEV_BOTTOM_CROSS = 2 };
+
+typedef struct DevJob {
+    DevBox region;              /* pixels to write == the result's current_window */
+    int32_t full_x, full_y;     /* output full_window.min */
+    int32_t out_pitch;
+    int32_t bottom_mode;        /* DEV_BOTTOM_* */
+    void *out16;                /* rgba_f16 or NULL */
+    void *out32;                /* rgba_f32 or NULL */
+    void *out8;                 /* rgba_u8 or NULL */
+    const uint8_t *u8tab;
+    float mix_a, mix_b;         /* crossfade weights (mix_a = 1 - mix_b computed once in f32) */
+    float single_alpha;         /* alpha scale of a single bottom source (1 unless copy_frame_alpha) */
+    int32_t n_layers;
+    /* work decomposition: items of PX pixels, item (row, i) covers x = item_x0 + i*PX .. */
+    int32_t item_x0;
+    uint32_t items_per_row, rows, total_items, div_magic;
+    DevSrc a, b;
+    DevLayer layer[CV_MAX_LAYERS];
+} DevJob;
+
+/* ---- argument blocks of the small kernels ---- */
+
+typedef struct EncodeArgs {
+    uint2 *frame; uint32_t *target; const uint16_t *srgb; const uint8_t *ramp;
+    int32_t pitch, ox, oy; DevBox win; uint32_t width, total, magic; int32_t write_back;
+} EncodeArgs;
+
+typedef struct ArgbArgs {
+    const uint2 *frame; uint32_t *out; const uint8_t *ramp45;
+    int32_t pitch, ox, oy; DevBox win; uint32_t width, total, magic;
+} ArgbArgs;
+
+typedef struct SubsampleArgs {
+    uint2 *frame; int32_t pitch, ox, oy;
+    uint8_t *plane[3]; int32_t stride[3];
+    int32_t layout, sub_shift, matrix, pic_x, pic_y;
+    int32_t wmin, wmax, row0, rows;         /* plane-local window */
+    int32_t tx0; uint32_t tx_count, total, magic;
+    const uint16_t *lut;                    /* linear -> Rec.709 */
+} SubsampleArgs;
+
+typedef struct LookupWindowArgs {
+    uint2 *frame; int32_t pitch, ox, oy; DevBox win; uint32_t width, total, magic; const uint16_t *lut;
+} LookupWindowArgs;
+
+typedef struct OverF32Args {
+    float4 *out; const float4 *b;
+    int32_t out_pitch, out_ox, out_oy, b_pitch, b_ox, b_oy;
+    DevBox out_cw, b_cw, region; float mix; uint32_t width, total, magic;
+} OverF32Args;
+
+/* Kernel shape selectors */
+enum { KB_LAYERS = 0,           /* no bottom sources: layer[0] is fetched, the rest go over it */
+       KB_GENERAL = 1,          /* bottom from a/b (f16 or f32 sources), no table needed */
+       KB_CODED = 2,            /* bottom from a/b with at least one coded source: 128 KiB table in SMEM */
+       KB_COUNT = 3 };
+
+/* ---- per-device state -------------------------------------------------------------- */
+
+typedef struct CvDevice {
+    int ready;
+    int index;
+    int sm_count;
+    size_t l2_bytes;
+    cudaStream_t stream;                /* library default stream */
+    half *lut[CV_LUT_COUNT];            /* device copies, 65536 entries each */
+    uint8_t *gamma45;                   /* device copy */
+    void *flush_buf; size_t flush_bytes;
+    DevJob *job_ring_dev;               /* device ring for batched job descriptors */
+    DevJob *job_ring_host;              /* pinned mirror */
+    uint32_t job_ring_size, job_ring_pos;
+    cudaEvent_t *job_ring_events;       /* one per ring segment */
+    pthread_mutex_t lock;               /* guards the job ring and the pool */
+} CvDevice;
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+CvDevice *cvi_device( void );                       /* current device state or NULL (sets last error) */
+int cvi_fail( int code, const char *fmt, ... );     /* records the message, returns code */
+int cvi_cuda( cudaError_t e, const char *what );    /* 0 or CV_ERR_CUDA */
+cudaStream_t cvi_stream( cv_stream s );
+void cvi_count_launch( unsigned n );
+
+/* pooled device allocations (cv_pool.cu) */
+int cvi_pool_alloc( void **ptr, size_t bytes );
+int cvi_pool_free( void *ptr );
+void cvi_pool_release_all( int device );
+
+/* kernels (cv_kernels.cu) */
+int cvi_launch_jobs( int shape, int px /*1|2*/, const DevJob *host_jobs, int count, cudaStream_t stream );
+int cvi_launch_half_from_float( half *out, const float *in, size_t count, cudaStream_t stream );
+int cvi_launch_half_to_float( float *out, const half *in, size_t count, cudaStream_t stream );
+int cvi_launch_lookup( const half *table, half *out, const half *in, size_t count, cudaStream_t stream );
+int cvi_launch_flush( void *buf, size_t bytes, cudaStream_t stream );
+int cvi_launch_encode_u8( const EncodeArgs *args, cudaStream_t stream );
+int cvi_launch_to_argb32( const ArgbArgs *args, cudaStream_t stream );
+int cvi_launch_subsample( const SubsampleArgs *args, cudaStream_t stream );
+int cvi_launch_lookup_window( const LookupWindowArgs *args, cudaStream_t stream );
+int cvi_launch_over_f32( const OverF32Args *args, cudaStream_t stream );
+int cvi_kernels_init( void );                       /* per-device function attributes */
+uint32_t cvi_div_magic( uint32_t d );
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif

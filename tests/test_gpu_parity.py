@@ -1,0 +1,240 @@
+"""GPU parity: the sm_100a path (through the C-ABI, libcanvas_b200.so) against the CPU oracle
+(oracle/liboracle.so, itself pinned bit-for-bit against the reference's own C code).
+
+Bar: bit-exact for 8-bit / integer outputs and window boxes; f16 RGBA is ASSERTED bit-exact too
+(the contract in BASELINE.json is <= 1 half ulp, max abs error <= 2^-10 on [0,1]; the ulp report
+is printed on failure).
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oraclelib as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    from canvas_b200 import device
+    device.init(0)
+    return device
+
+
+def half_ulp_distance(a, b):
+    """Distance in representable halves between raw half bit patterns (sign-magnitude aware)."""
+    def key(x):
+        x = x.astype(np.int32)
+        return np.where(x & 0x8000, -(x & 0x7FFF), x & 0x7FFF)
+    return np.abs(key(a) - key(b))
+
+
+def assert_frames_equal(gpu_array, gpu_window, host_frame, what):
+    assert tuple(gpu_window) == host_frame.current.tuple(), "%s: window %r != oracle %r" % (what, tuple(gpu_window), host_frame.current)
+    if host_frame.current.empty:
+        return
+    b = host_frame.current
+    f = host_frame.full
+    ys = slice(b.min_y - f.min_y, b.max_y - f.min_y + 1)
+    xs = slice(b.min_x - f.min_x, b.max_x - f.min_x + 1)
+    got, want = gpu_array[ys, xs], host_frame.array[ys, xs]
+    if not np.array_equal(got, want):
+        d = half_ulp_distance(got, want)
+        bad = np.argwhere(d > 0)
+        y, x, c = bad[0]
+        raise AssertionError("%s: %d of %d halves differ, max %d ulp; first at (x=%d,y=%d,c=%d): gpu %04x oracle %04x"
+                             % (what, len(bad), got.size, d.max(), x + b.min_x, y + b.min_y, c, got[y, x, c], want[y, x, c]))
+
+
+def to_device(dev, hf):
+    return dev.DeviceFrame16.from_numpy(hf.array, hf.full.tuple(), hf.current.tuple())
+
+
+def poisoned(dev, full):
+    f = dev.DeviceFrame16(full)
+    f.fill(0x5A)
+    return f
+
+
+# ------------------------------------------------------------------ composite
+
+COMPOSITE_CASES = {
+    # name: (full, [layer (full, current)])
+    "two_full": ((0, 0, 63, 47), [((0, 0, 63, 47), (0, 0, 63, 47))] * 2),
+    "eight_full": ((0, 0, 127, 63), [((0, 0, 127, 63), (0, 0, 127, 63))] * 8),
+    "single": ((0, 0, 31, 15), [((0, 0, 31, 15), (2, 3, 20, 9))]),
+    "partial_windows": ((0, 0, 95, 63), [((0, 0, 95, 63), (0, 0, 95, 63)), ((0, 0, 95, 63), (10, 5, 60, 40)),
+                                         ((0, 0, 95, 63), (31, 20, 95, 63)), ((0, 0, 95, 63), (3, 50, 40, 60))]),
+    "odd_origins": ((-3, -1, 60, 40), [((-3, -1, 60, 40), (-3, -1, 60, 40)), ((-7, -5, 71, 51), (-5, 0, 33, 17)),
+                                       ((1, 2, 50, 30), (1, 2, 50, 30))]),
+    "disjoint": ((0, 0, 63, 63), [((0, 0, 63, 63), (0, 0, 9, 9)), ((0, 0, 63, 63), (20, 20, 29, 29)),
+                                  ((0, 0, 63, 63), (5, 5, 24, 24))]),
+    "outside_full": ((0, 0, 39, 29), [((0, 0, 39, 29), (0, 0, 39, 29)), ((-20, -10, 59, 49), (-20, -10, 10, 12)),
+                                      ((30, 20, 90, 70), (30, 20, 90, 70)), ((100, 100, 120, 120), (100, 100, 120, 120))]),
+    "empty_bottom": ((0, 0, 31, 31), [((0, 0, 31, 31), (0, 0, -1, -1)), ((0, 0, 31, 31), (4, 4, 20, 20)),
+                                      ((0, 0, 31, 31), (8, 1, 30, 12))]),
+    "odd_width": ((0, 0, 44, 20), [((0, 0, 44, 20), (0, 0, 44, 20)), ((0, 0, 44, 20), (7, 3, 33, 18))]),
+    "sixteen": ((0, 0, 63, 31), [((0, 0, 63, 31), (i, i % 5, 63 - i, 31 - (i % 3))) for i in range(16)]),
+}
+
+
+@pytest.mark.parametrize("name", sorted(COMPOSITE_CASES))
+def test_composite_over_matches_oracle(dev, name):
+    full, specs = COMPOSITE_CASES[name]
+    layers = [O.synth_frame(lf, 100 + i, cw) for i, (lf, cw) in enumerate(specs)]
+
+    want = O.HostFrame16(full)
+    want.array[:] = 0x5A5A
+    arr = (O.Frame16 * len(layers))(*[l.c for l in layers])
+    O.oracle().orc_composite_f16(C.byref(want.c), arr, len(layers))
+
+    dlayers = [to_device(dev, l) for l in layers]
+    out = poisoned(dev, full)
+    dev.composite_over(out, dlayers)
+    assert_frames_equal(out.download(), out.current.tuple(), want, "composite/" + name)
+
+    # pixels outside the result window must not have been written
+    got = out.download()
+    mask = np.ones(got.shape[:2], bool)
+    if not want.current.empty:
+        b, f = want.current, want.full
+        mask[b.min_y - f.min_y: b.max_y - f.min_y + 1, b.min_x - f.min_x: b.max_x - f.min_x + 1] = False
+    assert np.all(got[mask] == 0x5A5A), "composite/%s wrote outside current_window" % name
+
+
+def test_composite_empty_inputs(dev):
+    out = poisoned(dev, (0, 0, 15, 15))
+    dev.composite_over(out, [])
+    assert out.current.empty
+    layer = to_device(dev, O.synth_frame((0, 0, 15, 15), 3, (0, 0, -1, -1)))
+    dev.composite_over(out, [layer, layer])
+    assert out.current.empty
+
+
+def test_composite_deep_stack_chains_without_extra_rounding(dev):
+    full = (0, 0, 47, 31)
+    layers = [O.synth_frame(full, 500 + i, (i % 7, i % 5, 47 - (i % 4), 31 - (i % 6))) for i in range(37)]
+    want = O.HostFrame16(full)
+    arr = (O.Frame16 * len(layers))(*[l.c for l in layers])
+    O.oracle().orc_composite_f16(C.byref(want.c), arr, len(layers))
+    out = poisoned(dev, full)
+    dev.composite_over(out, [to_device(dev, l) for l in layers])
+    assert_frames_equal(out.download(), out.current.tuple(), want, "composite/deep")
+
+
+# ------------------------------------------------------------------ crossfade
+
+@pytest.mark.parametrize("mix", [0.0, 1.0, 0.25, 0.5, 0.999, 1e-3, -0.5, 1.5, float("nan")])
+@pytest.mark.parametrize("windows", [((0, 0, 63, 35), (0, 0, 63, 35)), ((0, 0, 40, 35), (10, 4, 63, 20)),
+                                     ((0, 0, 9, 9), (20, 20, 29, 29)), ((0, 0, -1, -1), (3, 3, 30, 30)),
+                                     ((5, 0, 20, 20), (2, 10, 25, 15))])
+def test_cross_matches_oracle(dev, mix, windows):
+    full = (0, 0, 63, 35)
+    a = O.synth_frame(full, 11, windows[0])
+    b = O.synth_frame(full, 12, windows[1])
+    want = O.HostFrame16(full)
+    O.oracle().orc_cross_f16(C.byref(want.c), C.byref(a.c), C.byref(b.c), mix)
+
+    out = poisoned(dev, full)
+    dev.mix_cross(out, to_device(dev, a), to_device(dev, b), mix)
+    assert_frames_equal(out.download(), out.current.tuple(), want, "cross mix=%r windows=%r" % (mix, windows))
+
+
+# ------------------------------------------------------------------ conversion
+
+def device_coded(dev, pic, zero=False):
+    return dev.DeviceCoded(pic.planes, pic.width, pic.height, pic.sub_x, pic.layout, pic.matrix, pic.pic, zero=zero)
+
+
+CONVERT_CASES = [
+    # width, height, sub_x, layout, matrix, pic, full, stride_pad, full_range
+    (720, 480, 4, O.LAYOUT_PLANAR, O.MATRIX_709, (0, -1), (0, -1, 719, 478), 0, False),      # the reference's own DV case
+    (720, 480, 4, O.LAYOUT_PLANAR, O.MATRIX_709, (0, -1), (-10, -10, 400, 200), 16, True),
+    (96, 40, 2, O.LAYOUT_PLANAR, O.MATRIX_709, (0, 0), (0, 0, 95, 39), 0, True),
+    (96, 40, 2, O.LAYOUT_UYVY, O.MATRIX_709, (0, 0), (0, 0, 95, 39), 0, True),
+    (96, 40, 2, O.LAYOUT_YUY2, O.MATRIX_601, (0, 0), (0, 0, 95, 39), 8, True),
+    (97, 33, 2, O.LAYOUT_PLANAR, O.MATRIX_601, (3, -2), (0, 0, 120, 40), 3, True),           # odd width, odd offset
+    (97, 33, 2, O.LAYOUT_UYVY, O.MATRIX_709, (-5, 1), (0, 0, 63, 63), 0, True),
+    (50, 20, 1, O.LAYOUT_PLANAR, O.MATRIX_709, (1, 1), (0, 0, 63, 31), 0, True),             # 4:4:4
+    (101, 17, 4, O.LAYOUT_PLANAR, O.MATRIX_601, (2, 0), (0, 0, 127, 31), 1, True),
+    (64, 16, 2, O.LAYOUT_PLANAR, O.MATRIX_709, (200, 200), (0, 0, 63, 31), 0, False),        # picture outside the frame
+]
+
+
+@pytest.mark.parametrize("case", CONVERT_CASES, ids=lambda c: "%dx%d_s%d_l%d_m%d" % c[:5])
+def test_convert_matches_oracle(dev, case):
+    w, h, sub, layout, matrix, pic, full, pad, full_range = case
+    picture = O.synth_coded(w, h, 7, sub, layout, matrix, pic, pad, full_range)
+    want = O.HostFrame16(full)
+    O.oracle().orc_reconstruct(C.byref(want.c), C.byref(picture.c))
+
+    out = poisoned(dev, full)
+    dev.convert_ycbcr8(out, device_coded(dev, picture))
+    assert_frames_equal(out.download(), out.current.tuple(), want, "convert %r" % (case,))
+
+
+def test_convert_all_byte_values(dev):
+    """Every (Y', C) byte pair appears: 256x256 picture with Y = x, Cb = y, Cr = 255 - y (4:4:4)."""
+    pic = O.CodedPicture(256, 256, 1, O.LAYOUT_PLANAR, O.MATRIX_709)
+    yy, xx = np.mgrid[0:256, 0:256].astype(np.uint8)
+    pic.set_samples(xx, yy, (255 - yy).astype(np.uint8))
+    want = O.HostFrame16((0, 0, 255, 255))
+    O.oracle().orc_reconstruct(C.byref(want.c), C.byref(pic.c))
+    out = poisoned(dev, (0, 0, 255, 255))
+    dev.convert_ycbcr8(out, device_coded(dev, pic))
+    assert_frames_equal(out.download(), out.current.tuple(), want, "convert/all-bytes")
+
+
+# ------------------------------------------------------------------ fused timeline frame
+
+@pytest.mark.parametrize("mix", [0.0, 0.3, 1.0])
+@pytest.mark.parametrize("layout", [O.LAYOUT_PLANAR, O.LAYOUT_UYVY])
+def test_timeline_frame_matches_oracle(dev, mix, layout):
+    full = (0, 0, 127, 71)
+    pa = O.synth_coded(128, 72, 21, 2, layout, O.MATRIX_709, (0, 0), 0, True)
+    pb = O.synth_coded(120, 60, 22, 2, layout, O.MATRIX_601, (4, 6), 0, True)
+    overlays = [O.synth_frame(full, 31, (10, 10, 90, 50)), O.synth_frame((-8, -8, 140, 80), 32, (-8, 30, 140, 80)),
+                O.synth_frame(full, 33, (100, 0, 127, 71))]
+
+    want = O.HostFrame16(full)
+    arr = (O.Frame16 * len(overlays))(*[o.c for o in overlays])
+    O.oracle().orc_timeline_frame_f16(C.byref(want.c), C.byref(pa.c), C.byref(pb.c), mix, arr, len(overlays))
+
+    out = poisoned(dev, full)
+    job = dev.make_job(out=out, a=device_coded(dev, pa), b=device_coded(dev, pb), mix_b=mix,
+                       layers=[to_device(dev, o) for o in overlays])
+    dev.render_frames([job])
+    dev.sync()
+    assert_frames_equal(out.download(), out.current.tuple(), want, "timeline mix=%r layout=%d" % (mix, layout))
+
+
+def test_render_frames_batch_equals_single(dev):
+    """A batch (grid-walked jobs from device memory) gives the same pixels as one job per launch."""
+    full = (0, 0, 95, 53)
+    pics = [O.synth_coded(96, 54, 40 + i, 2, O.LAYOUT_UYVY, O.MATRIX_709, (0, 0), 0, True) for i in range(3)]
+    overlays = [O.synth_frame(full, 60 + i, (i * 3, i, 95 - i, 53 - 2 * i)) for i in range(4)]
+    dpics = [device_coded(dev, p) for p in pics]
+    dover = [to_device(dev, o) for o in overlays]
+
+    jobs, outs = [], []
+    for f in range(9):
+        out = poisoned(dev, full)
+        outs.append(out)
+        if f % 3 == 0:
+            jobs.append(dev.make_job(out=out, layers=[dover[f % 4], dover[(f + 1) % 4]]))
+        elif f % 3 == 1:
+            jobs.append(dev.make_job(out=out, a=dpics[f % 3], b=dpics[(f + 1) % 3], mix_b=f / 9.0, layers=[dover[f % 4]]))
+        else:
+            jobs.append(dev.make_job(out=out, a=dover[0], b=dover[1], mix_b=0.5, layers=[dover[2]]))
+    dev.render_frames(jobs)
+    dev.sync()
+    batch = [(o.download(), o.current.tuple()) for o in outs]
+
+    for f, job in enumerate(jobs):
+        outs[f].fill(0x5A)
+        dev.render_frames([job])
+        dev.sync()
+        single = outs[f].download()
+        assert batch[f][1] == outs[f].current.tuple()
+        assert np.array_equal(batch[f][0], single), "job %d differs between batch and single launch" % f
