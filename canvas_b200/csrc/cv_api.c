@@ -159,6 +159,7 @@ static int build_job( cv_frame_job *job, const BuildOptions *opt, DevJob *dj, in
     dj->out8 = job->out_u8;
     dj->u8tab = job->u8_table;
     dj->single_alpha = 1.0f;
+    dj->one = 1.0f;
 
     if( (job->out && !dj->out16) || (job->out_f32 && !dj->out32) )
         return cvi_fail( CV_ERR_ARGUMENT, "frame job: output frame without data" );
@@ -253,6 +254,23 @@ static int build_job( cv_frame_job *job, const BuildOptions *opt, DevJob *dj, in
 
     *px = pair_ok ? 2 : 1;
     *shape = coded ? KB_CODED : (dj->bottom_mode != DEV_BOTTOM_NONE ? KB_GENERAL : KB_LAYERS);
+
+    /* f32 frames keep the IEEE-division path (their results are visible at full f32 precision) */
+    if( dj->out32 || (dj->bottom_mode != DEV_BOTTOM_NONE && (dj->a.kind == CV_SRC_F32 ||
+            (dj->bottom_mode == DEV_BOTTOM_CROSS && dj->b.kind == CV_SRC_F32))) )
+        dj->flags |= JOB_FLAG_EXACT;
+
+    /* the common workspace case: full-coverage layers, no window tests needed in the kernel */
+    if( *shape == KB_LAYERS && *px == 2 && ((under.x0 - dj->full_x) & 1) == 0 && ((under.x1 - under.x0 + 1) & 1) == 0 ) {
+        int simple = 1;
+        for( int i = 0; i < n; i++ ) {
+            const DevBox *c = &dj->layer[i].cw;
+            if( c->x0 != under.x0 || c->y0 != under.y0 || c->x1 != under.x1 || c->y1 != under.y1 || dj->layer[i].mix != 1.0f )
+                simple = 0;
+        }
+        if( simple )
+            dj->flags |= JOB_FLAG_SIMPLE;
+    }
 
     if( *px == 2 ) {
         dj->item_x0 = dj->full_x + ((under.x0 - dj->full_x) & ~1);

@@ -52,6 +52,8 @@ typedef struct DevJob {
     float mix_a, mix_b;         /* crossfade weights (mix_a = 1 - mix_b computed once in f32) */
     float single_alpha;         /* alpha scale of a single bottom source (1 unless copy_frame_alpha) */
     int32_t n_layers;
+    int32_t flags;              /* JOB_FLAG_* (cv_kernels.cu) */
+    float one;                  /* 1.0f, opaque to the compiler (see add2_unfused in cv_kernels.cu) */
     /* work decomposition: items of PX pixels, item (row, i) covers x = item_x0 + i*PX .. */
     int32_t item_x0;
     uint32_t items_per_row, rows, total_items, div_magic;
@@ -89,6 +91,9 @@ typedef struct OverF32Args {
     int32_t out_pitch, out_ox, out_oy, b_pitch, b_ox, b_oy;
     DevBox out_cw, b_cw, region; float mix; uint32_t width, total, magic;
 } OverF32Args;
+
+enum { JOB_FLAG_SIMPLE = 1,     /* every layer covers the whole region, mix == 1, no bottom: no window tests */
+       JOB_FLAG_EXACT = 2 };    /* f32 frames involved: IEEE-division path only */
 
 /* Kernel shape selectors */
 enum { KB_LAYERS = 0,           /* no bottom sources: layer[0] is fetched, the rest go over it */

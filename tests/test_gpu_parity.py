@@ -31,9 +31,12 @@ def half_ulp_distance(a, b):
 
 
 def assert_frames_equal(gpu_array, gpu_window, host_frame, what):
-    assert tuple(gpu_window) == host_frame.current.tuple(), "%s: window %r != oracle %r" % (what, tuple(gpu_window), host_frame.current)
+    gx0, gy0, gx1, gy1 = tuple(gpu_window)
     if host_frame.current.empty:
+        # "empty <=> max < min" (framework.h:80-82); the reference does not canonicalise empty boxes
+        assert gx1 < gx0 or gy1 < gy0, "%s: window %r, oracle says empty" % (what, tuple(gpu_window))
         return
+    assert tuple(gpu_window) == host_frame.current.tuple(), "%s: window %r != oracle %r" % (what, tuple(gpu_window), host_frame.current)
     b = host_frame.current
     f = host_frame.full
     ys = slice(b.min_y - f.min_y, b.max_y - f.min_y + 1)
@@ -238,3 +241,62 @@ def test_render_frames_batch_equals_single(dev):
         single = outs[f].download()
         assert batch[f][1] == outs[f].current.tuple()
         assert np.array_equal(batch[f][0], single), "job %d differs between batch and single launch" % f
+
+
+# ------------------------------------------------------------------ values outside the fast path's range
+
+def assert_equal_up_to_nan_payload(got, want, what):
+    """Bit-exact, except that any NaN matches any NaN (x86 propagates payloads, the GPU canonicalises)."""
+    nan_g = ((got & 0x7C00) == 0x7C00) & ((got & 0x03FF) != 0)
+    nan_w = ((want & 0x7C00) == 0x7C00) & ((want & 0x03FF) != 0)
+    same = (got == want) | (nan_g & nan_w)
+    if not same.all():
+        bad = np.argwhere(~same)
+        y, x, c = bad[0]
+        raise AssertionError("%s: %d halves differ; first at (%d,%d,%d): gpu %04x oracle %04x"
+                             % (what, len(bad), x, y, c, got[y, x, c], want[y, x, c]))
+
+
+@pytest.mark.parametrize("kind", ["negative_and_zero_signs", "alpha_above_one", "inf_and_huge", "any_bits"])
+def test_composite_unusual_values_take_the_exact_path(dev, kind):
+    full = (0, 0, 127, 31)
+    rng = np.random.default_rng(hash(kind) % 1000)
+    layers = []
+    for i in range(5):
+        f = O.synth_frame(full, 900 + i)
+        a = f.array
+        pick = rng.random(a.shape[:2]) < 0.3
+        if kind == "negative_and_zero_signs":
+            a[pick, 0] |= 0x8000                                  # negative red
+            a[rng.random(a.shape[:2]) < 0.2, 1] = 0x8000          # -0.0 green
+            a[rng.random(a.shape[:2]) < 0.2, 3] = 0x3C00
+        elif kind == "alpha_above_one":
+            a[pick, 3] = rng.integers(0x3C01, 0x4400, size=int(pick.sum()), dtype=np.uint16)
+            a[rng.random(a.shape[:2]) < 0.1, 3] = 0xB800          # alpha -0.5
+        elif kind == "inf_and_huge":
+            a[pick, 2] = 0x7C00
+            a[rng.random(a.shape[:2]) < 0.1, 0] = 0x7BFF
+            a[rng.random(a.shape[:2]) < 0.1, 3] = 0x7C00
+        else:
+            a[pick] = rng.integers(0, 65536, size=(int(pick.sum()), 4), dtype=np.uint16)
+        layers.append(f)
+
+    want = O.HostFrame16(full)
+    arr = (O.Frame16 * len(layers))(*[l.c for l in layers])
+    O.oracle().orc_composite_f16(C.byref(want.c), arr, len(layers))
+    out = poisoned(dev, full)
+    dev.composite_over(out, [to_device(dev, l) for l in layers])
+    assert out.current.tuple() == want.current.tuple()
+    assert_equal_up_to_nan_payload(out.download(), want.array, "composite/" + kind)
+
+
+def test_composite_large_random_stack_bit_exact(dev):
+    """8 full 1080p layers: ~16.6 M divisions per layer through the shared-reciprocal fast path."""
+    full = (0, 0, 1919, 1079)
+    layers = [O.synth_frame(full, 700 + i) for i in range(8)]
+    want = O.HostFrame16(full)
+    arr = (O.Frame16 * 8)(*[l.c for l in layers])
+    O.oracle().orc_composite_f16(C.byref(want.c), arr, 8)
+    out = poisoned(dev, full)
+    dev.composite_over(out, [to_device(dev, l) for l in layers])
+    assert_frames_equal(out.download(), out.current.tuple(), want, "composite/1080p x8")

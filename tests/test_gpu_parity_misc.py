@@ -211,5 +211,7 @@ def test_copy_frame_f16(dev):
     want = O.HostFrame16((0, 0, 47, 31))
     O.oracle().orc_copy_frame_f16(C.byref(want.c), C.byref(src.c))
     out = poisoned(dev, (0, 0, 47, 31))
-    dev.check(dev.lib().cv_copy_frame_f16(C.byref(out.c), C.byref(to_device(dev, src).c), None))
+    dsrc = to_device(dev, src)
+    dev.check(dev.lib().cv_copy_frame_f16(C.byref(out.c), C.byref(dsrc.c), None))
+    dev.sync()
     assert_frames_equal(out.download(), out.current.tuple(), want, "copy_frame_f16")
