@@ -235,6 +235,7 @@ static int build_job( cv_frame_job *job, const BuildOptions *opt, DevJob *dj, in
         d->pitch = box_width( &L->frame.full_window );
         d->ox = L->frame.full_window.min.x;
         d->oy = L->frame.full_window.min.y;
+        d->origin = (const char *) d->data - ((int64_t) d->oy * d->pitch + d->ox) * (int64_t) sizeof(rgba_f16);
         d->mix = mix;
         d->cw = cw;
         d->under = under;

@@ -32,6 +32,7 @@ typedef struct DevSrc {
 
 typedef struct DevLayer {
     const void *data;           /* f16 pixels */
+    const void *origin;         /* data - (oy * pitch + ox) pixels: the address pixel (0,0) would have */
     int32_t pitch, ox, oy;
     float mix;
     DevBox cw;                  /* clipped to the output's full_window; never empty (empty layers are dropped) */
