@@ -45,6 +45,8 @@ static int same_window( const box2i *a, const box2i *b ) {
 
 /* ------------------------------------------------------------- job builder */
 
+static void f16_bounds( const void *data, const box2i *full, const void **lo, const void **hi );
+
 typedef struct BuildOptions {
     int pull_short_circuit;     /* crossfade: mix 0 / 1 fetch one source only (video_mix.c:50-55) */
     float single_alpha;         /* alpha scale when the bottom is one source (copy_frame_alpha) */
@@ -66,6 +68,8 @@ static int fill_source( DevSrc *d, const cv_source *s, const DevBox *full ) {
             d->pitch = box_width( &s->f16.full_window );
             d->ox = s->f16.full_window.min.x;
             d->oy = s->f16.full_window.min.y;
+            d->origin = (const char *) d->data - ((int64_t) d->oy * d->pitch + d->ox) * (int64_t) sizeof(rgba_f16);
+            f16_bounds( d->data, &s->f16.full_window, &d->lo, &d->hi );
             if( !dev_empty( &d->cw ) && (!d->data || ((uintptr_t) d->data & 7)) )
                 return cvi_fail( CV_ERR_ARGUMENT, "f16 source: data is NULL or not 8-byte aligned" );
             return CV_OK;
@@ -121,6 +125,14 @@ static int fill_source( DevSrc *d, const cv_source *s, const DevBox *full ) {
 
 static int f16_pair_ok( const void *data, int pitch, int ox, int full_x ) {
     return ((uintptr_t) data & 15) == 0 && (pitch & 1) == 0 && (((int64_t) ox - full_x) & 1) == 0;
+}
+
+/* the 16-byte aligned part of a frame's allocation: bulk copies of whole pixel pairs must stay inside it */
+static void f16_bounds( const void *data, const box2i *full, const void **lo, const void **hi ) {
+    const int w = box_width( full ), h = full->max.y < full->min.y ? 0 : full->max.y - full->min.y + 1;
+    const uintptr_t begin = (uintptr_t) data, end = begin + (uintptr_t) w * (uintptr_t) h * sizeof(rgba_f16);
+    *lo = (const void *)( (begin + 15) & ~(uintptr_t) 15 );
+    *hi = (const void *)( end & ~(uintptr_t) 15 );
 }
 
 /*
@@ -236,6 +248,7 @@ static int build_job( cv_frame_job *job, const BuildOptions *opt, DevJob *dj, in
         d->ox = L->frame.full_window.min.x;
         d->oy = L->frame.full_window.min.y;
         d->origin = (const char *) d->data - ((int64_t) d->oy * d->pitch + d->ox) * (int64_t) sizeof(rgba_f16);
+        f16_bounds( d->data, &L->frame.full_window, &d->lo, &d->hi );
         d->mix = mix;
         d->cw = cw;
         d->under = under;
@@ -271,6 +284,19 @@ static int build_job( cv_frame_job *job, const BuildOptions *opt, DevJob *dj, in
         }
         if( simple )
             dj->flags |= JOB_FLAG_SIMPLE;
+    }
+
+    /* the row-segment kernel also moves f16 bottom sources as aligned pixel pairs */
+    if( *px == 2 && !(dj->flags & JOB_FLAG_EXACT) ) {
+        int seg = 1;
+        if( dj->bottom_mode != DEV_BOTTOM_NONE && dj->a.kind == CV_SRC_F16 )
+            seg = seg && f16_pair_ok( dj->a.data, dj->a.pitch, dj->a.ox, dj->full_x );
+        if( dj->bottom_mode == DEV_BOTTOM_CROSS && dj->b.kind == CV_SRC_F16 )
+            seg = seg && f16_pair_ok( dj->b.data, dj->b.pitch, dj->b.ox, dj->full_x );
+        if( dj->out8 && !dj->out16 && (dj->out_pitch & 1) )
+            seg = 0;
+        if( seg )
+            dj->flags |= JOB_FLAG_SEG;
     }
 
     if( *px == 2 ) {

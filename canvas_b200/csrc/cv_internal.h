@@ -22,6 +22,8 @@ typedef struct DevSrc {
     int32_t pitch;              /* pixels per row of the f16/f32 frame */
     int32_t ox, oy;             /* full_window.min of the f16/f32 frame */
     const void *data;           /* f16 or f32 pixels */
+    const void *origin;         /* f16: data - (oy * pitch + ox) pixels */
+    const void *lo, *hi;        /* f16: the 16-byte aligned byte range [lo, hi) inside the frame's allocation */
     DevBox cw;                  /* valid pixels, already clipped to the output's full_window */
     /* CV_SRC_CODED */
     const uint8_t *plane[3];
@@ -33,6 +35,7 @@ typedef struct DevSrc {
 typedef struct DevLayer {
     const void *data;           /* f16 pixels */
     const void *origin;         /* data - (oy * pitch + ox) pixels: the address pixel (0,0) would have */
+    const void *lo, *hi;        /* the 16-byte aligned byte range [lo, hi) inside the frame's allocation (bulk copies stay inside) */
     int32_t pitch, ox, oy;
     float mix;
     DevBox cw;                  /* clipped to the output's full_window; never empty (empty layers are dropped) */
@@ -94,7 +97,8 @@ typedef struct OverF32Args {
 } OverF32Args;
 
 enum { JOB_FLAG_SIMPLE = 1,     /* every layer covers the whole region, mix == 1, no bottom: no window tests */
-       JOB_FLAG_EXACT = 2 };    /* f32 frames involved: IEEE-division path only */
+       JOB_FLAG_EXACT = 2,      /* f32 frames involved: IEEE-division path only */
+       JOB_FLAG_SEG = 4 };      /* every f16 input is pair-aligned with the output: the row-segment kernel (k_seg) applies */
 
 /* Kernel shape selectors */
 enum { KB_LAYERS = 0,           /* no bottom sources: layer[0] is fetched, the rest go over it */
