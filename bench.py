@@ -251,7 +251,7 @@ def run_ours(args):
     name = args.workload
     w, h, bytes_per_px, description = WORKLOADS[name]
     frame_bytes = w * h * bytes_per_px
-    batch = name in ("1080p_convert", "1080p_cross_u8", "4k_convert") and not args.no_batch    # microsecond kernels: one launch per step
+    batch = not args.no_batch      # one cv_render_frames() call per step (the library launches one kernel per frame)
 
     base = make_base(dev, name, 1234 + rank)
     n_sets = max(INPUT_SETS, int(np.ceil(RING_BYTES / frame_bytes)))

@@ -86,6 +86,40 @@ class FrameJob(C.Structure):
                 ("out_u8", C.c_void_p), ("u8_table", C.c_void_p), ("full_window", Box2i), ("current_window", Box2i)]
 
 
+class Clip(C.Structure):
+    """cv_clip"""
+    _fields_ = [("frames", C.POINTER(Source)), ("count", C.c_int32), ("reserved", C.c_int32)]
+
+
+class TimelineItem(C.Structure):
+    """cv_timeline_item"""
+    _fields_ = [("x", C.c_int64), ("length", C.c_int64), ("z", C.c_int64), ("offset", C.c_int64),
+                ("clips", C.POINTER(Clip)), ("clips_b", C.POINTER(Clip)), ("mix_first", C.c_float), ("mix_last", C.c_float),
+                ("ramp_start", C.c_int64), ("ramp_length", C.c_int64)]
+
+
+class TimelineTarget(C.Structure):
+    """cv_timeline_target"""
+    _fields_ = [("out", C.POINTER(FrameF16)), ("out_u8", C.POINTER(C.c_void_p)), ("u8_table", C.c_void_p),
+                ("ring", C.c_int32), ("reserved", C.c_int32)]
+
+
+TIMELINE_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int64, C.POINTER(FrameJob), C.c_void_p)
+
+
+class TimelineRun(C.Structure):
+    """cv_timeline_run"""
+    _fields_ = [("items", C.POINTER(TimelineItem)), ("item_count", C.c_int32), ("n_gpus", C.c_int32),
+                ("devices", C.POINTER(C.c_int32)), ("first", C.c_int64), ("last", C.c_int64), ("chunk", C.c_int32),
+                ("reserved", C.c_int32), ("targets", C.POINTER(TimelineTarget)), ("sink", TIMELINE_SINK), ("user", C.c_void_p)]
+
+
+class TimelineStats(C.Structure):
+    """cv_timeline_stats"""
+    _fields_ = [("device", C.c_int32), ("reserved", C.c_int32), ("frames", C.c_int64), ("launches", C.c_uint64),
+                ("device_ms", C.c_double), ("wall_ms", C.c_double)]
+
+
 _PROTOTYPES = {
     # name: (restype, argtypes)
     "cv_device_count": (C.c_int, []),
@@ -137,10 +171,17 @@ _PROTOTYPES = {
     "cv_mix_over_f32": (C.c_int, [C.POINTER(FrameF32), C.POINTER(FrameF32), C.c_float, C.c_void_p]),
     "cv_frame_f16_to_f32": (C.c_int, [C.POINTER(FrameF32), C.POINTER(FrameF16), C.c_void_p]),
     "cv_frame_f32_to_f16": (C.c_int, [C.POINTER(FrameF16), C.POINTER(FrameF32), C.c_void_p]),
+    "cv_solid_frame_f16": (C.c_int, [C.POINTER(FrameF16), C.POINTER(Box2i), C.POINTER(C.c_float), C.c_void_p]),
+    "cv_solid_frame_f32": (C.c_int, [C.POINTER(FrameF32), C.POINTER(Box2i), C.POINTER(C.c_float), C.c_void_p]),
     "cv_upload_display_table": (C.c_int, [C.c_float, C.POINTER(C.c_void_p)]),
     "cv_encode_u8": (C.c_int, [C.POINTER(FrameF16), C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "cv_to_argb32": (C.c_int, [C.POINTER(FrameF16), C.c_void_p, C.c_void_p]),
     "cv_render_frames": (C.c_int, [C.POINTER(FrameJob), C.c_int, C.c_void_p]),
+    "cv_timeline_showing": (C.c_int, [C.POINTER(TimelineItem), C.c_int, C.c_int64, C.POINTER(C.c_int), C.c_int]),
+    "cv_timeline_job": (C.c_int, [C.POINTER(TimelineItem), C.c_int, C.c_int, C.c_int64, C.POINTER(FrameJob)]),
+    "cv_timeline_device_of": (C.c_int, [C.c_int64, C.c_int64, C.c_int, C.c_int]),
+    "cv_timeline_frames_of": (C.c_int64, [C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_int]),
+    "cv_timeline_render": (C.c_int, [C.POINTER(TimelineRun), C.POINTER(TimelineStats)]),
 }
 
 _lib = None

@@ -535,6 +535,55 @@ int cv_frame_f32_to_f16( rgba_frame_f16 *out, const rgba_frame_f32 *in, cv_strea
     return cv_render_frames( &job, 1, stream );
 }
 
+/* ------------------------------------------------------------- solid colour */
+
+/* half.c:47-51 as bit operations (truncation, subnormals kept): four values on the host */
+static uint16_t f2h_bits( float value ) {
+    union { float f; uint32_t u; } v = { .f = value };
+    const uint32_t sign = (v.u >> 16) & 0x8000u, mant = v.u & 0x007FFFFFu;
+    const int e = (int)((v.u >> 23) & 0xFF) - 127;
+    if( e < -24 ) return (uint16_t) sign;
+    if( e < -14 ) return (uint16_t)(sign | ((0x0400u >> (-14 - e)) + (mant >> (-e - 1))));
+    if( e <= 15 ) return (uint16_t)(sign | (((uint32_t)(e + 15) << 10) + (mant >> 13)));
+    if( e < 128 ) return (uint16_t)(sign | 0x7C00u);
+    return (uint16_t)(sign | (0x7C00u + (mant >> 13)));
+}
+
+static int solid_fill( void *data, const box2i *full, box2i *current, const box2i *window, int bytes, const uint32_t word[4], cv_stream stream ) {
+    if( !cvi_device() ) { box2i_set_empty( current ); return CV_ERR_NOT_INITIALISED; }
+    box2i_intersect( current, window, full );
+    if( box2i_is_empty( current ) )
+        return CV_OK;
+    if( !data ) { box2i_set_empty( current ); return cvi_fail( CV_ERR_ARGUMENT, "cv_solid_frame: frame without data" ); }
+
+    FillArgs A;
+    memset( &A, 0, sizeof(A) );
+    A.data = data; A.pitch = box_width( full ); A.ox = full->min.x; A.oy = full->min.y; A.bytes = bytes;
+    A.win = to_dev( current );
+    A.width = (uint32_t) box_width( current );
+    A.total = A.width * (uint32_t)( current->max.y - current->min.y + 1 );
+    A.magic = cvi_div_magic( A.width );
+    memcpy( A.word, word, sizeof(A.word) );
+    int rc = cvi_launch_fill( &A, cvi_stream( stream ) );
+    if( rc ) box2i_set_empty( current );
+    return rc;
+}
+
+int cv_solid_frame_f16( rgba_frame_f16 *frame, const box2i *window, const float color[4], cv_stream stream ) {
+    if( !frame || !window || !color ) return cvi_fail( CV_ERR_ARGUMENT, "cv_solid_frame_f16: NULL argument" );
+    /* SolidColorVideoSource.c:67-68: the f32 colour is truncated to half once, then replicated */
+    const uint32_t word[4] = { (uint32_t) f2h_bits( color[0] ) | ((uint32_t) f2h_bits( color[1] ) << 16),
+                               (uint32_t) f2h_bits( color[2] ) | ((uint32_t) f2h_bits( color[3] ) << 16), 0, 0 };
+    return solid_fill( frame->data, &frame->full_window, &frame->current_window, window, 8, word, stream );
+}
+
+int cv_solid_frame_f32( rgba_frame_f32 *frame, const box2i *window, const float color[4], cv_stream stream ) {
+    if( !frame || !window || !color ) return cvi_fail( CV_ERR_ARGUMENT, "cv_solid_frame_f32: NULL argument" );
+    uint32_t word[4];
+    memcpy( word, color, sizeof(word) );
+    return solid_fill( frame->data, &frame->full_window, &frame->current_window, window, 16, word, stream );
+}
+
 /* --------------------------------------------------- half arrays and tables */
 
 int cv_half_from_float( half *out, const float *in, size_t count, cv_stream stream ) {

@@ -96,6 +96,10 @@ typedef struct OverF32Args {
     DevBox out_cw, b_cw, region; float mix; uint32_t width, total, magic;
 } OverF32Args;
 
+typedef struct FillArgs {
+    void *data; int32_t pitch, ox, oy, bytes; DevBox win; uint32_t width, total, magic; uint32_t word[4];
+} FillArgs;
+
 enum { JOB_FLAG_SIMPLE = 1,     /* every layer covers the whole region, mix == 1, no bottom: no window tests */
        JOB_FLAG_EXACT = 2,      /* f32 frames involved: IEEE-division path only */
        JOB_FLAG_SEG = 4 };      /* every f16 input is pair-aligned with the output: the row-segment kernel (k_seg) applies */
@@ -150,6 +154,7 @@ int cvi_launch_to_argb32( const ArgbArgs *args, cudaStream_t stream );
 int cvi_launch_subsample( const SubsampleArgs *args, cudaStream_t stream );
 int cvi_launch_lookup_window( const LookupWindowArgs *args, cudaStream_t stream );
 int cvi_launch_over_f32( const OverF32Args *args, cudaStream_t stream );
+int cvi_launch_fill( const FillArgs *args, cudaStream_t stream );
 int cvi_kernels_init( void );                       /* per-device function attributes */
 uint32_t cvi_div_magic( uint32_t d );
 

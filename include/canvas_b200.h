@@ -182,6 +182,11 @@ int cv_mix_over_f32( rgba_frame_f32 *out, const rgba_frame_f32 *b, float mix_b, 
 int cv_frame_f16_to_f32( rgba_frame_f32 *out, const rgba_frame_f16 *in, cv_stream stream );
 int cv_frame_f32_to_f16( rgba_frame_f16 *out, const rgba_frame_f32 *in, cv_stream stream );
 
+/* SolidColorVideoSource (src/process/SolidColorVideoSource.c:52-103): current_window = window
+ * intersected with full_window, every pixel of it = color (f16: truncated to half once). */
+int cv_solid_frame_f16( rgba_frame_f16 *frame, const box2i *window, const float color[4], cv_stream stream );
+int cv_solid_frame_f32( rgba_frame_f32 *frame, const box2i *window, const float color[4], cv_stream stream );
+
 /* Display encode: target[px] = ramp[ sRGB[ frame[px] ] ] per channel (alpha too) over
  * frame->current_window; target is full_window-sized.  `u8_table` is a device copy of the
  * COMPOSED table from cv_upload_display_table().  With write_back != 0 the sRGB-encoded
@@ -228,6 +233,86 @@ typedef struct {
 /* Renders `count` independent jobs with as few launches as their shapes allow
  * (jobs of one shape share a launch: grid.y = job). */
 int cv_render_frames( cv_frame_job *jobs, int count, cv_stream stream );
+
+/* ------------------------------------------- frame-parallel multi-GPU timeline */
+
+/*
+ * The reference renders a timeline one frame at a time on one thread
+ * (workspace_get_frame_f32, src/cprocess/workspace.c:494-550).  A frame depends only on its
+ * index, so here a range of frames is partitioned over the GPUs of one box with no collective:
+ * gpu slot = ((frame - first) / chunk) mod n_gpus, one host thread and one stream per GPU.
+ *
+ * A clip is a device-resident ring of sources (one ring PER GPU: frames are produced where their
+ * inputs live); source frame i of a clip is frames[i mod count].
+ */
+typedef struct {
+    const cv_source *frames;
+    int32_t count;
+    int32_t reserved;
+} cv_clip;
+
+/* One workspace item (workspace_add_item, framework.h:573; workspace.c:309-345): shown at frames
+ * x <= f < x + length, stacked by ascending z, reading its clip at f - x + offset.  With clips_b the
+ * item is the crossfade VideoMixFilter(clips, clips_b, mix_b) where mix_b ramps linearly from
+ * mix_first at source frame ramp_start to mix_last at ramp_start + ramp_length (a two-point linear
+ * AnimationFunc, src/process/AnimationFunc.c:439-446: interpolated in double, then (float)).
+ * Only the bottom item showing at a frame may be a crossfade or a coded / f32 source. */
+typedef struct {
+    int64_t x, length, z, offset;
+    const cv_clip *clips;           /* [n_gpus] */
+    const cv_clip *clips_b;         /* [n_gpus] or NULL */
+    float mix_first, mix_last;
+    int64_t ramp_start, ramp_length;
+} cv_timeline_item;
+
+/* Indices (into items) of the items showing at `frame`, bottom first; returns how many show. */
+int cv_timeline_showing( const cv_timeline_item *items, int count, int64_t frame, int *indices, int capacity );
+/* Fills job->a, b, mix_b, layers, layer_count for `frame` on GPU slot `slot` (outputs are left to
+ * the caller); returns the number of items showing (0 = empty frame) or a negative cv_err.  Pure
+ * host logic: usable without a GPU. */
+int cv_timeline_job( const cv_timeline_item *items, int count, int slot, int64_t frame, cv_frame_job *job );
+/* The partition: which GPU slot renders `frame`, and how many frames of [first, last] a slot gets. */
+int cv_timeline_device_of( int64_t frame, int64_t first, int chunk, int n_gpus );
+int64_t cv_timeline_frames_of( int slot, int64_t first, int64_t last, int chunk, int n_gpus );
+
+/* Per-GPU outputs: a ring of device frames (and optionally 8-bit targets) reused round-robin. */
+typedef struct {
+    rgba_frame_f16 *out;            /* [ring] device frames from cv_frame_alloc_f16 on that GPU */
+    rgba_u8 **out_u8;               /* [ring] device buffers or NULL */
+    const uint8_t *u8_table;        /* that GPU's composed display table (cv_upload_display_table) */
+    int32_t ring;
+    int32_t reserved;
+} cv_timeline_target;
+
+/* Called on the GPU's own host thread right after frame `frame` was enqueued on `stream`; it may
+ * enqueue copies out of job->out / job->out_u8 on the same stream (the ring slot is not reused before
+ * they finish).  Frames of one GPU arrive in ascending order; different GPUs call concurrently. */
+typedef int (*cv_timeline_sink)( void *user, int slot, int64_t frame, const cv_frame_job *job, cv_stream stream );
+
+typedef struct {
+    const cv_timeline_item *items;
+    int32_t item_count;
+    int32_t n_gpus;
+    const int32_t *devices;         /* [n_gpus] CUDA ordinals, or NULL for 0..n_gpus-1 */
+    int64_t first, last;            /* inclusive */
+    int32_t chunk;                  /* consecutive frames per GPU turn (8..32 keeps input rings warm) */
+    int32_t reserved;
+    const cv_timeline_target *targets;  /* [n_gpus] */
+    cv_timeline_sink sink;          /* may be NULL */
+    void *user;
+} cv_timeline_run;
+
+typedef struct {
+    int32_t device;
+    int32_t reserved;
+    int64_t frames;
+    uint64_t launches;
+    double device_ms;               /* CUDA events around this GPU's share, on its stream */
+    double wall_ms;
+} cv_timeline_stats;
+
+/* Renders frames first..last; blocks until every GPU has finished.  stats: [n_gpus] or NULL. */
+int cv_timeline_render( const cv_timeline_run *run, cv_timeline_stats *stats );
 
 #if defined(__cplusplus)
 }
