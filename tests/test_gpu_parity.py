@@ -300,3 +300,65 @@ def test_composite_large_random_stack_bit_exact(dev):
     out = poisoned(dev, full)
     dev.composite_over(out, [to_device(dev, l) for l in layers])
     assert_frames_equal(out.download(), out.current.tuple(), want, "composite/1080p x8")
+
+
+# ------------------------------------------------------------------ same-signature batches (persistent k_seg)
+
+@pytest.mark.parametrize("shape", ["convert", "cross_u8", "timeline", "layers_u8"])
+def test_uniform_batch_matches_oracle(dev, shape):
+    """Runs of jobs with one signature go through ONE persistent launch (k_seg BATCH); every frame is
+    checked against the oracle, and the launch count proves the batch form was taken."""
+    w, h = 200, 37                      # 100 pairs per row: a short last segment in every row
+    full = (0, 0, w - 1, h - 1)
+    orc = O.oracle()
+    n = 7
+    pics_a = [O.synth_coded(w, h, 500 + i, 2, O.LAYOUT_UYVY, O.MATRIX_709, (0, 0), 0, True) for i in range(n)]
+    pics_b = [O.synth_coded(w, h, 600 + i, 2, O.LAYOUT_UYVY, O.MATRIX_709, (0, 0), 0, True) for i in range(n)]
+    frames = [O.synth_frame(full, 700 + i, full) for i in range(n + 3)]
+    dev_a, dev_b = [device_coded(dev, p) for p in pics_a], [device_coded(dev, p) for p in pics_b]
+    dev_f = [to_device(dev, f) for f in frames]
+    table = dev.display_table(1.25)
+    srgb, ramp = np.zeros(65536, np.uint16), np.zeros(65536, np.uint8)
+    orc.orc_build_lut(O.LUT_LINEAR_TO_SRGB, O.ptr(srgb))
+    orc.orc_build_intent_ramp(1.25, O.ptr(ramp))
+
+    jobs, outs, u8s, wants, want_u8 = [], [], [], [], []
+    for i in range(n):
+        want = O.HostFrame16(full)
+        out = poisoned(dev, full)
+        u8 = None
+        if shape == "convert":
+            orc.orc_reconstruct(C.byref(want.c), C.byref(pics_a[i].c))
+            job = dev.make_job(out=out, a=dev_a[i])
+        elif shape == "cross_u8":
+            mix = 0.125 + 0.1 * i
+            orc.orc_cross_f16(C.byref(want.c), C.byref(frames[i].c), C.byref(frames[i + 1].c), mix)
+            u8 = dev.DeviceBuffer(w * h * 4)
+            job = dev.make_job(out=out, a=dev_f[i], b=dev_f[i + 1], mix_b=mix, out_u8=u8, u8_table=table)
+        elif shape == "timeline":
+            mix = 0.05 + 0.13 * i
+            layers = [frames[i + 1], frames[i + 2], frames[i + 3]]
+            arr = (O.Frame16 * 3)(*[l.c for l in layers])
+            orc.orc_timeline_frame_f16(C.byref(want.c), C.byref(pics_a[i].c), C.byref(pics_b[i].c), mix, arr, 3)
+            job = dev.make_job(out=out, a=dev_a[i], b=dev_b[i], mix_b=mix, layers=[dev_f[i + 1], dev_f[i + 2], dev_f[i + 3]])
+        else:
+            layers = [frames[i], frames[i + 1], frames[i + 2]]
+            arr = (O.Frame16 * 3)(*[l.c for l in layers])
+            orc.orc_composite_f16(C.byref(want.c), arr, 3)
+            u8 = dev.DeviceBuffer(w * h * 4)
+            job = dev.make_job(out=out, layers=[dev_f[i], dev_f[i + 1], dev_f[i + 2]], out_u8=u8, u8_table=table)
+        if u8 is not None:
+            copy = want.copy()
+            target = np.zeros((h, w, 4), np.uint8)
+            orc.orc_encode_u8(C.byref(copy.c), O.ptr(srgb), O.ptr(ramp), O.ptr(target))
+            want_u8.append(target)
+        jobs.append(job); outs.append(out); u8s.append(u8); wants.append(want)
+
+    before = dev.lib().cv_kernel_launches()
+    dev.render_frames(jobs)
+    dev.sync()
+    assert dev.lib().cv_kernel_launches() - before == 1, "the run was not taken as one batch launch"
+    for i in range(n):
+        assert_frames_equal(outs[i].download(), outs[i].current.tuple(), wants[i], "%s batch job %d" % (shape, i))
+        if u8s[i] is not None:
+            assert np.array_equal(u8s[i].download(np.uint8, (h, w, 4)), want_u8[i]), "%s batch job %d: 8-bit output" % (shape, i)
