@@ -10,9 +10,11 @@ Default workload (BASELINE.json: the configuration the metric is quoted on, BASE
 Other workloads (explicit --workload only; parity-test configurations, not the bench line):
     4k_composite_convert  bottom layer is an 8-bit 4:2:2 picture converted in-kernel + 7 f16 layers (66 B/px)
     4k_convert            4:2:2 Rec.709 -> linear f16 RGBA (10 B/px)
-    1080p_convert         same at 1920x1080 (BASELINE.json configs[0])
+    1080p_convert         same at 1920x1080 (BASELINE.json configs[0]); 1080p_convert_planar: Y, Cb, Cr planes
     1080p_cross_u8        two f16 sources crossfaded, display-encoded to 8-bit (20 B/px)
     4k_timeline           2 x (4:2:2 -> f16) -> crossfade -> + 3 overlays -> f16 (36 B/px at full coverage)
+    1080p_4layer_windows  4-layer workspace composite, layers 1-3 with partial windows (BASELINE.json configs[2];
+                          bytes = 8 x (sum of layer window areas + output area) = 56.1 MB per frame)
 
 A "step" renders FRAMES_PER_STEP frames (one kernel launch per frame) from a ring of input sets, each
 larger than L2.  `value` is device-resident throughput (CUDA events on the launching stream);
@@ -54,12 +56,27 @@ WORKLOADS = {
     "4k_composite_convert": (3840, 2160, 66, "3840x2160 4:2:2 bottom converted in-kernel + 7 f16 layers -> f16"),
     "4k_convert": (3840, 2160, 10, "3840x2160 8-bit 4:2:2 Rec.709 -> linear f16 RGBA"),
     "1080p_convert": (1920, 1080, 10, "1920x1080 8-bit 4:2:2 Rec.709 -> linear f16 RGBA"),
+    "1080p_convert_planar": (1920, 1080, 10, "1920x1080 8-bit planar 4:2:2 Rec.709 (Y, Cb, Cr planes) -> linear f16 RGBA"),
     "1080p_cross_u8": (1920, 1080, 20, "1920x1080 two-source f16 crossfade -> 8-bit display encode"),
     "4k_timeline": (3840, 2160, 36, "3840x2160 2x(4:2:2->f16) crossfade + 3 f16 overlays -> f16"),
+    "1080p_4layer_windows": (1920, 1080, None, "1920x1080 4-layer alpha-over workspace composite, partial layer windows -> f16"),
 }
 
 
 # ----------------------------------------------------------------------------- synthetic inputs
+
+# layer windows of 1080p_4layer_windows (layer 0 covers the frame); inclusive corners
+WINDOWS_1080P = [(0, 0, 1919, 1079), (200, 100, 1719, 979), (480, 0, 1919, 700), (0, 540, 959, 1079)]
+
+
+def workload_bytes(name):
+    """Algorithmic bytes per frame: every input pixel read once, every output pixel written once."""
+    w, h, per_px, _ = WORKLOADS[name]
+    if per_px is not None:
+        return w * h * per_px
+    area = lambda b: (b[2] - b[0] + 1) * (b[3] - b[1] + 1)
+    return 8 * (sum(area(b) for b in WINDOWS_1080P) + w * h)
+
 
 def synth_layer(rng, h, w):
     """Raw half bits: rgb uniform halves in [0,1], alpha from {0,1/4,1/2,3/4,1,1} or a random fraction."""
@@ -137,21 +154,27 @@ class InputSet:
         self.out_u8 = None
         self.d2h_bytes = w * h * 8
 
-        def add_layer(i):
+        def add_layer(i, window=None):
             arr = np.roll(base["layer"][i % len(base["layer"])], 17 * len(self.layers) + 1, axis=1)
-            frame = dev.DeviceFrame16.from_numpy(arr, full)
+            frame = dev.DeviceFrame16.from_numpy(arr, full, window)
             pinned = PinnedArray(dev, arr.shape, np.uint16)
             pinned.array[...] = arr
             self.layers.append(frame)
             self.uploads.append((frame.c.data, pinned))
 
-        def add_coded(i):
+        def add_coded(i, planar=False):
             arr = np.roll(base["uyvy"][i % len(base["uyvy"])], 4 * (len(self.coded) + 1), axis=1)
-            pic = dev.DeviceCoded([arr], w, h, 2, dev.CV_LAYOUT_UYVY, dev.CV_MATRIX_709)
-            pinned = PinnedArray(dev, arr.shape, np.uint8)
-            pinned.array[...] = arr
+            if planar:          # the same samples as three planes: UYVY = Cb Y0 Cr Y1
+                planes = [np.ascontiguousarray(arr[:, 1::2]), np.ascontiguousarray(arr[:, 0::4]), np.ascontiguousarray(arr[:, 2::4])]
+                pic = dev.DeviceCoded(planes, w, h, 2, dev._abi.CV_LAYOUT_PLANAR, dev.CV_MATRIX_709)
+            else:
+                planes = [arr]
+                pic = dev.DeviceCoded(planes, w, h, 2, dev.CV_LAYOUT_UYVY, dev.CV_MATRIX_709)
             self.coded.append(pic)
-            self.uploads.append((pic.buffers[0].ptr, pinned))
+            for buffer, plane in zip(pic.buffers, planes):
+                pinned = PinnedArray(dev, plane.shape, np.uint8)
+                pinned.array[...] = plane
+                self.uploads.append((buffer.ptr, pinned))
 
         if name == "4k_8layer_composite":
             for i in range(8):
@@ -162,8 +185,8 @@ class InputSet:
             for i in range(7):
                 add_layer(i)
             self.job = dev.make_job(out=self.out, a=self.coded[0], layers=self.layers)
-        elif name in ("4k_convert", "1080p_convert"):
-            add_coded(0)
+        elif name in ("4k_convert", "1080p_convert", "1080p_convert_planar"):
+            add_coded(0, planar=name.endswith("planar"))
             self.job = dev.make_job(out=self.out, a=self.coded[0])
         elif name == "1080p_cross_u8":
             add_layer(0)
@@ -179,6 +202,10 @@ class InputSet:
             for i in range(3):
                 add_layer(i)
             self.job = dev.make_job(out=self.out, a=self.coded[0], b=self.coded[1], mix_b=0.375, layers=self.layers)
+        elif name == "1080p_4layer_windows":
+            for i, window in enumerate(WINDOWS_1080P):
+                add_layer(i, window)
+            self.job = dev.make_job(out=self.out, layers=self.layers)
         else:
             raise SystemExit("unknown workload %r" % name)
 
@@ -249,8 +276,8 @@ def run_ours(args):
     lib = dev.lib()
 
     name = args.workload
-    w, h, bytes_per_px, description = WORKLOADS[name]
-    frame_bytes = w * h * bytes_per_px
+    w, h, _, description = WORKLOADS[name]
+    frame_bytes = workload_bytes(name)
     batch = not args.no_batch      # one cv_render_frames() call per step (the library launches one kernel per frame)
 
     base = make_base(dev, name, 1234 + rank)
@@ -409,7 +436,8 @@ def cpu_run(name, frames, threads):
     # oracle port, frame-parallel through a thread pool (ctypes releases the GIL)
     from concurrent.futures import ThreadPoolExecutor
     orc = O.oracle()
-    layers = [O.HostFrame16(full, full, synth_layer(rng, h, w)) for _ in range(8 if "8layer" in name else (7 if "composite" in name else 3))]
+    layers = [O.HostFrame16(full, full, synth_layer(rng, h, w)) for _ in range(8 if "8layer" in name else (7 if "composite" in name else (4 if "4layer" in name else 3)))]
+    windowed = [O.HostFrame16(full, win, l.array) for l, win in zip(layers, WINDOWS_1080P)] if name == "1080p_4layer_windows" else []
     pics = [O.synth_coded(w, h, 5 + i, 2, O.LAYOUT_UYVY, O.MATRIX_709) for i in range(2)]
     srgb, ramp = np.zeros(65536, np.uint16), np.zeros(65536, np.uint8)
     orc.orc_build_lut(O.LUT_LINEAR_TO_SRGB, O.ptr(srgb))
@@ -425,7 +453,7 @@ def cpu_run(name, frames, threads):
         elif name == "4k_composite_convert":
             arr = (O.Frame16 * 7)(*[l.c for l in layers[:7]])
             orc.orc_timeline_frame_f16(C.byref(out.c), C.byref(pics[0].c), None, 0.0, arr, 7)
-        elif name in ("4k_convert", "1080p_convert"):
+        elif name in ("4k_convert", "1080p_convert", "1080p_convert_planar"):
             orc.orc_reconstruct(C.byref(out.c), C.byref(pics[0].c))
         elif name == "1080p_cross_u8":
             orc.orc_cross_f16(C.byref(out.c), C.byref(layers[0].c), C.byref(layers[1].c), 0.375)
@@ -433,6 +461,9 @@ def cpu_run(name, frames, threads):
         elif name == "4k_timeline":
             arr = (O.Frame16 * 3)(*[l.c for l in layers[:3]])
             orc.orc_timeline_frame_f16(C.byref(out.c), C.byref(pics[0].c), C.byref(pics[1].c), 0.375, arr, 3)
+        elif name == "1080p_4layer_windows":
+            arr = (O.Frame16 * 4)(*[l.c for l in windowed])
+            orc.orc_composite_f16(C.byref(out.c), arr, 4)
 
     def worker(slot):
         n = frames // threads + (1 if slot < frames % threads else 0)

@@ -6,6 +6,7 @@ Bar: bit-exact for 8-bit / integer outputs and window boxes; f16 RGBA is ASSERTE
 is printed on failure).
 """
 import ctypes as C
+import os
 
 import numpy as np
 import pytest
@@ -357,7 +358,8 @@ def test_uniform_batch_matches_oracle(dev, shape):
     before = dev.lib().cv_kernel_launches()
     dev.render_frames(jobs)
     dev.sync()
-    assert dev.lib().cv_kernel_launches() - before == 1, "the run was not taken as one batch launch"
+    if not os.environ.get("CV_SEG_NO_UNIFORM") and not os.environ.get("CV_NO_SEG_BATCH"):
+        assert dev.lib().cv_kernel_launches() - before == 1, "the run was not taken as one batch launch"
     for i in range(n):
         assert_frames_equal(outs[i].download(), outs[i].current.tuple(), wants[i], "%s batch job %d" % (shape, i))
         if u8s[i] is not None:
