@@ -62,6 +62,11 @@ class FrameF32(C.Structure):
     _fields_ = [("data", C.c_void_p), ("full_window", Box2i), ("current_window", Box2i)]
 
 
+class V2f(C.Structure):
+    """v2f: passed by value"""
+    _fields_ = [("x", C.c_float), ("y", C.c_float)]
+
+
 class Coded(C.Structure):
     """cv_coded"""
     _fields_ = [("plane", C.c_void_p * 3), ("stride", C.c_int32 * 3), ("layout", C.c_int32),
@@ -173,6 +178,9 @@ _PROTOTYPES = {
     "cv_frame_f32_to_f16": (C.c_int, [C.POINTER(FrameF16), C.POINTER(FrameF32), C.c_void_p]),
     "cv_solid_frame_f16": (C.c_int, [C.POINTER(FrameF16), C.POINTER(Box2i), C.POINTER(C.c_float), C.c_void_p]),
     "cv_solid_frame_f32": (C.c_int, [C.POINTER(FrameF32), C.POINTER(Box2i), C.POINTER(C.c_float), C.c_void_p]),
+    "cv_scale_bilinear_f32": (C.c_int, [C.POINTER(FrameF32), V2f, C.POINTER(FrameF32), V2f, V2f, C.c_void_p]),
+    "cv_gain_offset_f32": (C.c_int, [C.POINTER(FrameF32), C.c_float, C.c_float, C.c_void_p]),
+    "cv_weave_fields_f16": (C.c_int, [C.POINTER(FrameF16), C.POINTER(FrameF16), C.c_void_p]),
     "cv_upload_display_table": (C.c_int, [C.c_float, C.POINTER(C.c_void_p)]),
     "cv_encode_u8": (C.c_int, [C.POINTER(FrameF16), C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "cv_to_argb32": (C.c_int, [C.POINTER(FrameF16), C.c_void_p, C.c_void_p]),

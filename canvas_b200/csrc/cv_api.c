@@ -584,6 +584,51 @@ int cv_solid_frame_f32( rgba_frame_f32 *frame, const box2i *window, const float 
     return solid_fill( frame->data, &frame->full_window, &frame->current_window, window, 16, word, stream );
 }
 
+/* ------------------------------------------------- gain / offset, field weave */
+
+int cv_gain_offset_f32( rgba_frame_f32 *frame, float gain, float offset, cv_stream stream ) {
+    if( !frame ) return cvi_fail( CV_ERR_ARGUMENT, "cv_gain_offset_f32: NULL frame" );
+    if( !cvi_device() ) return CV_ERR_NOT_INITIALISED;
+    box2i cw;
+    box2i_intersect( &cw, &frame->current_window, &frame->full_window );
+    if( box2i_is_empty( &cw ) ) return CV_OK;
+    if( !frame->data ) return cvi_fail( CV_ERR_ARGUMENT, "cv_gain_offset_f32: frame without data" );
+
+    FillArgs A;
+    memset( &A, 0, sizeof(A) );
+    A.data = frame->data; A.pitch = box_width( &frame->full_window ); A.ox = frame->full_window.min.x; A.oy = frame->full_window.min.y;
+    A.bytes = 16; A.win = to_dev( &cw );
+    A.width = (uint32_t) box_width( &cw );
+    A.total = A.width * (uint32_t)( cw.max.y - cw.min.y + 1 );
+    A.magic = cvi_div_magic( A.width );
+    memcpy( &A.word[0], &gain, 4 );
+    memcpy( &A.word[1], &offset, 4 );
+    return cvi_launch_gain_offset( &A, cvi_stream( stream ) );
+}
+
+int cv_weave_fields_f16( rgba_frame_f16 *frame, const rgba_frame_f16 *even_rows, cv_stream stream ) {
+    /* Pulldown23RemovalFilter.c:83-101: the even rows of frame's current window are replaced by the same rows
+     * of `even_rows` (the copy engine does the strided row copy; pixels are untouched bits) */
+    if( !frame || !even_rows ) return cvi_fail( CV_ERR_ARGUMENT, "cv_weave_fields_f16: NULL argument" );
+    if( !cvi_device() ) return CV_ERR_NOT_INITIALISED;
+    box2i cw;
+    box2i_intersect( &cw, &frame->current_window, &even_rows->current_window );
+    box2i_intersect( &cw, &cw, &frame->full_window );
+    if( box2i_is_empty( &cw ) ) return CV_OK;
+
+    const int first = (cw.min.y + 1) & ~1;
+    if( first > cw.max.y ) return CV_OK;
+    const size_t rows = (size_t)( (cw.max.y - first) / 2 + 1 );
+    const size_t dpitch = (size_t) box_width( &frame->full_window ) * sizeof(rgba_f16);
+    const size_t spitch = (size_t) box_width( &even_rows->full_window ) * sizeof(rgba_f16);
+    const char *src = (const char *) even_rows->data + (size_t)( first - even_rows->full_window.min.y ) * spitch
+                    + (size_t)( cw.min.x - even_rows->full_window.min.x ) * sizeof(rgba_f16);
+    char *dst = (char *) frame->data + (size_t)( first - frame->full_window.min.y ) * dpitch
+              + (size_t)( cw.min.x - frame->full_window.min.x ) * sizeof(rgba_f16);
+    return cvi_cuda( cudaMemcpy2DAsync( dst, 2 * dpitch, src, 2 * spitch, (size_t) box_width( &cw ) * sizeof(rgba_f16), rows,
+                                        cudaMemcpyDeviceToDevice, cvi_stream( stream ) ), "cudaMemcpy2DAsync(weave)" );
+}
+
 /* --------------------------------------------------- half arrays and tables */
 
 int cv_half_from_float( half *out, const float *in, size_t count, cv_stream stream ) {

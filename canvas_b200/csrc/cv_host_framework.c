@@ -473,6 +473,56 @@ void video_mix_cross_f32_pull( rgba_frame_f32 *out, video_source *a, int frame_a
     free( temp.data );
 }
 
+/* ------------------------------------------------------------------ scaler */
+
+void video_scale_bilinear_f32( rgba_frame_f32 *target, v2f target_point, rgba_frame_f32 *source, v2f source_point, v2f factors ) {
+    /* video_scale.c:231-285; the scaler zero-fills the whole target, so all of full_window comes back */
+    if( !host_ready() ) { box2i_set_empty( &target->current_window ); return; }
+
+    rgba_frame_f32 dt = { 0 }, ds = { 0 };
+    int rc = twin_f32( &dt, target, 0 );
+    if( !rc ) rc = twin_f32( &ds, source, 1 );
+    if( !rc ) rc = cv_scale_bilinear_f32( &dt, target_point, &ds, source_point, factors, NULL );
+    if( !rc ) {
+        const int identity = factors.x == 1.0f && factors.y == 1.0f && target_point.x == source_point.x && target_point.y == source_point.y;
+        target->current_window = dt.current_window;
+        rc = copy_window( target->data, dt.data, &target->full_window, identity ? &dt.current_window : &target->full_window,
+                          sizeof(rgba_f32), cudaMemcpyDeviceToHost );
+        if( !rc ) rc = cv_stream_sync( NULL );
+    }
+    if( rc ) box2i_set_empty( &target->current_window );
+    release_f32( &dt );
+    release_f32( &ds );
+}
+
+void video_scale_bilinear_f32_pull( rgba_frame_f32 *target, v2f target_point, video_source *source, int frame, box2i *source_rect, v2f source_point, v2f factors ) {
+    /* video_scale.c:287-319: fetch just the part of the source the target can see, then scale */
+    if( factors.x == 0.0f || factors.y == 0.0f ) {
+        box2i_set_empty( &target->current_window );
+        return;
+    }
+    if( factors.x == 1.0f && factors.y == 1.0f && target_point.x == source_point.x && target_point.y == source_point.y ) {
+        video_get_frame_f32( source, frame, target );
+        return;
+    }
+
+    rgba_frame_f32 temp;
+    const box2i tf = target->full_window;
+    box2i_set( &temp.full_window,
+        (int)( source_point.x - (target_point.x - (float) tf.min.x) / factors.x ) - 1,
+        (int)( source_point.y - (target_point.y - (float) tf.min.y) / factors.y ) - 1,
+        (int)( source_point.x + ((float) tf.max.x - target_point.x) / factors.x ) + 1,
+        (int)( source_point.y + ((float) tf.max.y - target_point.y) / factors.y ) + 1 );
+    box2i_intersect( &temp.full_window, &temp.full_window, source_rect );
+
+    temp.data = (rgba_f32 *) malloc( sizeof(rgba_f32) * (window_pixels( &temp.full_window ) + 1) );
+    if( !temp.data ) { box2i_set_empty( &target->current_window ); return; }
+
+    video_get_frame_f32( source, frame, &temp );
+    video_scale_bilinear_f32( target, target_point, &temp, source_point, factors );
+    free( temp.data );
+}
+
 /* ------------------------------------------------------------------ DV conversion */
 
 enum { DV_WIDTH = 720, DV_HEIGHT = 480, DV_SUB_X = 4, DV_PIC_X = 0, DV_PIC_Y = -1 };

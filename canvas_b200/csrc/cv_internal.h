@@ -100,6 +100,13 @@ typedef struct FillArgs {
     void *data; int32_t pitch, ox, oy, bytes; DevBox win; uint32_t width, total, magic; uint32_t word[4];
 } FillArgs;
 
+typedef struct ScaleArgs {
+    float4 *target; int32_t t_pitch, t_ox, t_oy; uint32_t t_width, total, magic;
+    const float4 *source; int32_t s_pitch, s_ox, s_oy;
+    int32_t vertical, cross_lo, cross_hi;
+    const int32_t *start, *src; const float *coef;       /* per target line: taps start[t]..start[t+1]-1 */
+} ScaleArgs;
+
 enum { JOB_FLAG_SIMPLE = 1,     /* every layer covers the whole region, mix == 1, no bottom: no window tests */
        JOB_FLAG_EXACT = 2,      /* f32 frames involved: IEEE-division path only */
        JOB_FLAG_SEG = 4 };      /* every f16 input is pair-aligned with the output: the row-segment kernel (k_seg) applies */
@@ -155,6 +162,8 @@ int cvi_launch_subsample( const SubsampleArgs *args, cudaStream_t stream );
 int cvi_launch_lookup_window( const LookupWindowArgs *args, cudaStream_t stream );
 int cvi_launch_over_f32( const OverF32Args *args, cudaStream_t stream );
 int cvi_launch_fill( const FillArgs *args, cudaStream_t stream );
+int cvi_launch_scale_axis( const ScaleArgs *args, cudaStream_t stream );
+int cvi_launch_gain_offset( const FillArgs *args, cudaStream_t stream );
 int cvi_kernels_init( void );                       /* per-device function attributes */
 uint32_t cvi_div_magic( uint32_t d );
 

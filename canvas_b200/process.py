@@ -560,6 +560,88 @@ class VideoWorkspace(VideoSource):
         return _Desc("stack", a=descs[0], layers=descs[1:])
 
 
+class VideoScaler(VideoSource):
+    """VideoScaler(source, target_point, source_point, scale_factors, source_rect): bilinear (triangle) resampling that
+    maps source_point onto target_point; every argument may be a frame function (VideoScaler.c:33-78, video_scale.c:287-319)."""
+
+    def __init__(self, source, target_point, source_point, scale_factors, source_rect):
+        self.source = source
+        self._target_point, self._source_point = _Holder(target_point), _Holder(source_point)
+        self._factors, self._rect = _Holder(scale_factors), _Holder(source_rect)
+
+    def _describe(self, frame_index, full):
+        if self.source is None:
+            return None
+        v2 = lambda holder: tuple(float(np.float32(v)) for v in holder.values(frame_index)[:2])
+        tp, sp, fac = v2(self._target_point), v2(self._source_point), v2(self._factors)
+        rect = self._rect.box(frame_index)
+        if fac[0] == 0.0 or fac[1] == 0.0:
+            return None
+        if fac == (1.0, 1.0) and tp == sp:
+            return self.source._describe(frame_index, full)
+        # the part of the source the target can see, computed with C's (int) truncation (video_scale.c:301-307)
+        f32, trunc = np.float32, lambda v: int(np.trunc(v))
+        want = box2i(trunc(f32(sp[0]) - (f32(tp[0]) - f32(full[0])) / f32(fac[0])) - 1,
+                     trunc(f32(sp[1]) - (f32(tp[1]) - f32(full[1])) / f32(fac[1])) - 1,
+                     trunc(f32(sp[0]) + (f32(full[2]) - f32(tp[0])) / f32(fac[0])) + 1,
+                     trunc(f32(sp[1]) + (f32(full[3]) - f32(tp[1])) / f32(fac[1])) + 1)
+        fetch = (max(want.min.x, rect.min.x), max(want.min.y, rect.min.y), min(want.max.x, rect.max.x), min(want.max.y, rect.max.y))
+        if fetch[2] < fetch[0] or fetch[3] < fetch[1]:
+            return None
+        src = dev.DeviceFrame32(fetch)
+        _run(self.source._describe(frame_index, fetch), fetch, out_f32=src)
+        out = dev.DeviceFrame32(full)
+        V = _abi.V2f
+        check(dev.lib().cv_scale_bilinear_f32(C.byref(out.c), V(*tp), C.byref(src.c), V(*sp), V(*fac), None), "cv_scale_bilinear_f32")
+        return None if out.current.empty else _Desc("f32", out)
+
+
+class VideoGainOffsetFilter(VideoSource):
+    """VideoGainOffsetFilter(source, gain, offset): rgb * gain + offset, alpha untouched (VideoGainOffsetFilter.c:66-82;
+    GL-only in the reference -- here an f32 pass on the device)."""
+
+    def __init__(self, source, gain, offset):
+        self.source = source
+        self._gain, self._offset = _Holder(gain), _Holder(offset)
+
+    def _describe(self, frame_index, full):
+        if self.source is None:
+            return None
+        frame = dev.DeviceFrame32(full)
+        _run(self.source._describe(frame_index, full), full, out_f32=frame)
+        if frame.current.empty:
+            return None
+        check(dev.lib().cv_gain_offset_f32(C.byref(frame.c), self._gain.f32(frame_index), self._offset.f32(frame_index), None),
+              "cv_gain_offset_f32")
+        return _Desc("f32", frame)
+
+
+class Pulldown23RemovalFilter(VideoSource):
+    """Pulldown23RemovalFilter(source, offset): 30 -> 24 fps; three of four output frames are whole source frames, the
+    fourth weaves the odd rows of one with the even rows of the next (Pulldown23RemovalFilter.c:46-105)."""
+
+    def __init__(self, source, offset):
+        self.source, self.offset = source, int(offset)
+
+    def _describe(self, frame_index, full):
+        if self.source is None:
+            return None
+        phase = (frame_index + 3) & 3 if self.offset == 4 else (frame_index + self.offset) & 3
+        base = ((frame_index + self.offset) >> 2) * 5 - self.offset
+        if phase != 2:
+            return self.source._describe(base + {0: 0, 1: 1, 3: 4}[phase], full)
+        frame = dev.DeviceFrame16(full)
+        _run(self.source._describe(base + 2, full), full, out=frame)
+        if frame.current.empty:
+            return None
+        window = frame.current.tuple()
+        other = dev.DeviceFrame16(window)
+        _run(self.source._describe(base + 3, window), window, out=other)
+        # the reference copies those rows whatever the second frame defined; rows it did not define are left as they are
+        check(dev.lib().cv_weave_fields_f16(C.byref(frame.c), C.byref(other.c), None), "cv_weave_fields_f16")
+        return _Desc("f16", frame)
+
+
 # ----------------------------------------------------------------------------- coded images (DV)
 
 class CodedImage:

@@ -187,6 +187,18 @@ int cv_frame_f32_to_f16( rgba_frame_f16 *out, const rgba_frame_f32 *in, cv_strea
 int cv_solid_frame_f16( rgba_frame_f16 *frame, const box2i *window, const float color[4], cv_stream stream );
 int cv_solid_frame_f32( rgba_frame_f32 *frame, const box2i *window, const float color[4], cv_stream stream );
 
+/* video_scale_bilinear_f32 (src/cprocess/video_scale.c:231-285) on device frames: separable triangle-filter
+ * resampling that maps source_point onto target_point with the given factors (> 1 enlarges).  The whole
+ * target full_window is written (zero where no tap reaches); current_window as the reference computes it. */
+int cv_scale_bilinear_f32( rgba_frame_f32 *target, v2f target_point, const rgba_frame_f32 *source, v2f source_point, v2f factors, cv_stream stream );
+
+/* video_filter_gain_offset_gl (src/cprocess/video_filter.c:27-72; a GLSL shader in the reference, no CPU twin):
+ * rgb = rgb * gain + offset over current_window, alpha untouched, in place. */
+int cv_gain_offset_f32( rgba_frame_f32 *frame, float gain, float offset, cv_stream stream );
+/* The field weave of Pulldown23RemovalFilter (src/process/Pulldown23RemovalFilter.c:83-101): the even rows of
+ * frame's current window are taken from `even_rows`. */
+int cv_weave_fields_f16( rgba_frame_f16 *frame, const rgba_frame_f16 *even_rows, cv_stream stream );
+
 /* Display encode: target[px] = ramp[ sRGB[ frame[px] ] ] per channel (alpha too) over
  * frame->current_window; target is full_window-sized.  `u8_table` is a device copy of the
  * COMPOSED table from cv_upload_display_table().  With write_back != 0 the sRGB-encoded

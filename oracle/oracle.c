@@ -12,6 +12,7 @@
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
+#include <stdint.h>
 
 /* ---- small box helpers (framework.h:80-137) -------------------------------- */
 static inline int imin( int a, int b ) { return a < b ? a : b; }
@@ -434,6 +435,115 @@ void orc_copy_frame_alpha_f32( orc_frame32 *out, const orc_frame32 *in, float al
                 row_out[x].a *= alpha;
         }
     }
+}
+
+/* ---- bilinear scaler: video_scale.c:24-285 -------------------------------------- */
+
+static orc_frame32 alloc32( const orc_box *full );
+
+/*
+ * One axis of the separable triangle-filter scaler (video_scale.c:33-126 vertical, :129-228
+ * horizontal), written once over "lines" (rows for the vertical pass, columns for the horizontal
+ * one).  Upsampling walks the SOURCE lines in ascending order and spreads each over the target
+ * lines its triangle reaches; downsampling walks the TARGET lines and gathers the source lines
+ * under its triangle, also ascending -- so every target pixel is  0 + in*c + in*c ...  with the
+ * source index increasing, products and sums rounded separately in f32.
+ */
+enum { ORC_SCALE_MAX_TAPS = 256 };
+
+static void scale_axis( orc_frame32 *target, float tmin, const orc_frame32 *source, float smin, float factor, int vertical ) {
+    const orc_box srect = source->current, trect = target->full;
+
+    /* the other axis: where source and target overlap (:36-37, :136-137) */
+    const int cross_lo = vertical ? imax( srect.min_x, trect.min_x ) : imax( srect.min_y, trect.min_y );
+    const int cross_hi = vertical ? imin( srect.max_x, trect.max_x ) : imin( srect.max_y, trect.max_y );
+    const int s_lo = vertical ? srect.min_y : srect.min_x, s_hi = vertical ? srect.max_y : srect.max_x;
+    const int t_lo = vertical ? trect.min_y : trect.min_x, t_hi = vertical ? trect.max_y : trect.max_x;
+
+    memset( target->data, 0, box_area( &trect ) * sizeof(orc_px32) );      /* video_fill_zero_f32, :24-31 */
+
+    if( factor == 1.0f && tmin == smin ) {                                  /* :44-47 */
+        orc_copy_frame_alpha_f32( target, source, 1.0f );
+        return;
+    }
+
+    int used_lo = INT32_MAX, used_hi = INT32_MIN;
+    float coeff[ORC_SCALE_MAX_TAPS];
+
+    const int upsample = factor > 1.0f;
+    const int outer_lo = upsample ? s_lo : t_lo, outer_hi = upsample ? s_hi : t_hi;
+
+    for( int outer = outer_lo; outer <= outer_hi; outer++ ) {
+        /* where this line falls on the other grid (:62, :94) */
+        const float where = upsample ? (outer - smin) * factor + tmin : (outer - tmin) / factor + smin;
+        const int base = (int) floorf( where );
+        int width = 0, center = 0;
+        if( orc_triangle( factor, where - base, coeff, ORC_SCALE_MAX_TAPS, &width, &center ) )
+            continue;
+
+        for( int tap = 0; tap < width; tap++ ) {
+            const int inner = base - center + tap;
+            const int t = upsample ? inner : outer, sidx = upsample ? outer : inner;
+
+            if( upsample ? (t < t_lo || t > t_hi) : (sidx < s_lo || sidx > s_hi) )
+                continue;
+
+            const float c = coeff[tap];
+            for( int k = cross_lo; k <= cross_hi; k++ ) {
+                const orc_px32 *in = vertical ? px32( source, k, sidx ) : px32( source, sidx, k );
+                orc_px32 *out = vertical ? px32( target, k, t ) : px32( target, t, k );
+                out->r += in->r * c;
+                out->g += in->g * c;
+                out->b += in->b * c;
+                out->a += in->a * c;
+            }
+
+            /* the horizontal pass only learns its extent inside the row loop (:185-186, :216-217) */
+            if( vertical || cross_lo <= cross_hi ) {
+                used_lo = imin( used_lo, t );
+                used_hi = imax( used_hi, t );
+            }
+        }
+    }
+
+    if( vertical ) { target->current.min_x = cross_lo; target->current.max_x = cross_hi; target->current.min_y = used_lo; target->current.max_y = used_hi; }
+    else           { target->current.min_x = used_lo; target->current.max_x = used_hi; target->current.min_y = cross_lo; target->current.max_y = cross_hi; }
+}
+
+/* video_scale_bilinear_f32, video_scale.c:231-285: one pass when the other axis is the identity, else the
+ * axis with the smaller factor first through a temporary whose window is computed with C's (int) truncation */
+void orc_scale_bilinear_f32( orc_frame32 *target, float tpx, float tpy, const orc_frame32 *source, float spx, float spy, float fx, float fy ) {
+    if( fx == 1.0f && tpx == spx ) {
+        if( fy == 1.0f && tpy == spy ) {
+            orc_copy_frame_alpha_f32( target, source, 1.0f );
+            return;
+        }
+        scale_axis( target, tpy, source, spy, fy, 1 );
+        return;
+    }
+    if( fy == 1.0f && tpy == spy ) {
+        scale_axis( target, tpx, source, spx, fx, 0 );
+        return;
+    }
+
+    orc_frame32 temp;
+    if( fx < fy ) {
+        orc_box want = { (int)( spx - (tpx - target->full.min_x) * fx ), source->current.min_y,
+                         (int)( spx + (target->full.max_x - tpx) * fx ), source->current.max_y };
+        want = box_intersect( &want, &target->full );
+        temp = alloc32( &want );
+        scale_axis( &temp, tpx, source, spx, fx, 0 );
+        scale_axis( target, tpy, &temp, spy, fy, 1 );
+    }
+    else {
+        orc_box want = { source->current.min_x, (int)( spy - (tpy - target->full.min_y) * fy ),
+                         source->current.max_x, (int)( spy + (target->full.max_y - tpy) * fy ) };
+        want = box_intersect( &want, &target->full );
+        temp = alloc32( &want );
+        scale_axis( &temp, tpy, source, spy, fy, 1 );
+        scale_axis( target, tpx, &temp, spx, fx, 0 );
+    }
+    free( temp.data );
 }
 
 /* ---- crossfade: video_mix.c:107-235 (intended window semantics) ------------------ */

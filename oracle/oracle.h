@@ -84,6 +84,8 @@ void orc_mix_cross_f32( orc_frame32 *out, const orc_frame32 *a, const orc_frame3
 void orc_mix_over_f32( orc_frame32 *out, const orc_frame32 *b, float mix_b );
 
 /* main.c:34-77 / 106-145 conversions between precisions over current_window */
+/* video_scale.c:231-285 (target_point, source_point, factors passed as scalars) */
+void orc_scale_bilinear_f32( orc_frame32 *target, float tpx, float tpy, const orc_frame32 *source, float spx, float spy, float fx, float fy );
 void orc_frame_f16_to_f32( orc_frame32 *out, const orc_frame16 *in );
 void orc_frame_f32_to_f16( orc_frame16 *out, const orc_frame32 *in );
 

@@ -193,6 +193,8 @@ def oracle():
         L.orc_copy_frame_alpha_f32.argtypes = [C.POINTER(Frame32), C.POINTER(Frame32), C.c_float]
         L.orc_mix_cross_f32.argtypes = [C.POINTER(Frame32), C.POINTER(Frame32), C.POINTER(Frame32), C.c_float]
         L.orc_mix_over_f32.argtypes = [C.POINTER(Frame32), C.POINTER(Frame32), C.c_float]
+        L.orc_scale_bilinear_f32.argtypes = [C.POINTER(Frame32), C.c_float, C.c_float, C.POINTER(Frame32), C.c_float, C.c_float,
+                                             C.c_float, C.c_float]
         L.orc_frame_f16_to_f32.argtypes = [C.POINTER(Frame32), C.POINTER(Frame16)]
         L.orc_frame_f32_to_f16.argtypes = [C.POINTER(Frame16), C.POINTER(Frame32)]
         L.orc_composite_f16.argtypes = [C.POINTER(Frame16), C.POINTER(Frame16), C.c_int]
@@ -229,7 +231,14 @@ def reference(fast=False):
     return _ref
 
 
+class V2f(C.Structure):
+    """v2f (include/framework.h): passed BY VALUE to video_scale_bilinear_f32."""
+    _fields_ = [("x", C.c_float), ("y", C.c_float)]
+
+
 def _set_ref_types(L):
+    L.video_scale_bilinear_f32.argtypes = [C.POINTER(Frame32), V2f, C.POINTER(Frame32), V2f, V2f]
+    L.video_scale_bilinear_f32.restype = None
     L.video_get_gamma45_ramp.restype = C.POINTER(C.c_uint8)
     for name in ("video_transfer_rec709_to_linear_scene", "video_transfer_rec709_to_linear_display",
                  "video_transfer_linear_to_rec709", "video_transfer_linear_to_sRGB"):
