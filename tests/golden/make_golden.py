@@ -17,6 +17,16 @@ sys.path.insert(0, os.path.dirname(HERE))
 import oraclelib as O  # noqa: E402
 
 
+# (fx, fy, target_point, source_point, source window, target full window)
+SCALE_GOLDEN = [
+    (2.0, 2.0, (0.0, 0.0), (0.0, 0.0), (0, 0, 39, 23), (0, 0, 79, 47)),
+    (1.0, 3.0, (2.0, 1.5), (2.0, -0.25), (3, 2, 50, 20), (-4, -6, 60, 70)),
+    (0.37, 1.0, (5.0, 0.0), (11.5, 0.0), (-10, 0, 90, 12), (0, -3, 44, 20)),
+    (1.7, 0.6, (10.0, 10.0), (20.25, 15.5), (0, 0, 63, 63), (-20, -20, 100, 60)),
+    (0.25, 3.5, (0.0, 0.0), (0.0, 0.0), (8, 4, 71, 19), (0, 0, 30, 80)),
+]
+
+
 def main():
     L = O.reference()
     out = {}
@@ -90,6 +100,17 @@ def main():
     L.ref_workspace_composite_f16(arr, z, 4, C.byref(res.c))
     out["workspace_window"] = np.array(res.current.tuple(), np.int32)
     out["workspace_pixels"] = res.array.copy()
+
+    # the scaler (video_scale.c:231-285): window + FNV of the whole target for a fixed list of cases
+    for i, (fx, fy, tp, sp, swin, tfull) in enumerate(SCALE_GOLDEN):
+        sfull = (swin[0] - 3, swin[1] - 2, swin[2] + 4, swin[3] + 1)
+        data = np.random.default_rng(700 + i).uniform(-0.5, 1.5, size=(sfull[3] - sfull[1] + 1, sfull[2] - sfull[0] + 1, 4)).astype(np.float32)
+        src = O.HostFrame32(sfull, swin, data)
+        dst = O.HostFrame32(tfull)
+        L.video_scale_bilinear_f32(C.byref(dst.c), O.V2f(*tp), C.byref(src.c), O.V2f(*sp), O.V2f(fx, fy))
+        out["scale_%d_window" % i] = np.array(dst.current.tuple(), np.int64)
+        out["scale_%d_fnv" % i] = np.uint32(O.fnv1a(dst.array))
+        out["scale_%d_row" % i] = dst.array[dst.array.shape[0] // 2].view(np.uint32).copy()
 
     np.savez_compressed(os.path.join(HERE, "reference_vectors.npz"), **out)
     print("wrote %d arrays" % len(out))
