@@ -41,6 +41,19 @@ INPUT_SETS = 3          # at least; small frames get more so that the ring of se
 RING_BYTES = 400e6      # >= 3 x the 126 MB L2
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per FRAME, from the committed `ncu --set full` captures
+# (profiles/r1_kernels.md, profiles/r1_composite.md); None where no capture exists or a frame fits L2 under ncu's single launch
+NCU_TRAFFIC_PER_FRAME = {
+    "4k_8layer_composite": 589.1e6, "4k_timeline": 4759e6 / 16, "4k_convert": 1267e6 / 16,
+    "4k_composite_convert": 8851e6 / 16, "1080p_cross_u8": 645e6 / 16,
+}
+
+
+def frames_per_step(workload):
+    """4K: 16 frames a step; 1080p: 120 (BASELINE.json configs[0] is quoted on 120 frames), so that a step is a few ms"""
+    return FRAMES_PER_STEP if workload.startswith("4k") else 120
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -279,6 +292,7 @@ def run_ours(args):
     w, h, _, description = WORKLOADS[name]
     frame_bytes = workload_bytes(name)
     batch = not args.no_batch      # one cv_render_frames() call per step (the library launches one kernel per frame)
+    FRAMES_PER_STEP = frames_per_step(name)
 
     base = make_base(dev, name, 1234 + rank)
     n_sets = max(INPUT_SETS, int(np.ceil(RING_BYTES / frame_bytes)))
@@ -368,7 +382,9 @@ def run_ours(args):
                    "l2": "inputs larger than L2 (%.0f MB per frame, %d rotating sets)" % (frame_bytes / 1e6, n_sets),
                    "sharding": "frames by index, one process per GPU, no collective"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_source, "algorithmic_bytes_per_frame": frame_bytes,
+                     "traffic": (NCU_TRAFFIC_PER_FRAME[name] * frames_per_launch if name in NCU_TRAFFIC_PER_FRAME else None),
+                     "traffic_source": "profiles/r1_kernels.md (ncu --set full, per frame x frames per launch)",
+                     "peak_source": peak_source, "algorithmic_bytes_per_frame": frame_bytes,
                      "kernel_ms": kernel_ms},
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": sets[0].h2d_bytes * FRAMES_PER_STEP,
                 "d2h_bytes_per_step": sets[0].d2h_bytes * FRAMES_PER_STEP, "steps": e2e_steps},

@@ -181,6 +181,10 @@ _PROTOTYPES = {
     "cv_scale_bilinear_f32": (C.c_int, [C.POINTER(FrameF32), V2f, C.POINTER(FrameF32), V2f, V2f, C.c_void_p]),
     "cv_gain_offset_f32": (C.c_int, [C.POINTER(FrameF32), C.c_float, C.c_float, C.c_void_p]),
     "cv_weave_fields_f16": (C.c_int, [C.POINTER(FrameF16), C.POINTER(FrameF16), C.c_void_p]),
+    "cv_color_rgb_to_xyz_sdtv": (C.c_int, [C.POINTER(FrameF16), C.c_void_p]),
+    "cv_color_xyz_to_srgb": (C.c_int, [C.POINTER(FrameF16), C.c_void_p]),
+    "cv_crop_f16": (C.c_int, [C.POINTER(FrameF16), C.POINTER(Box2i), C.c_void_p]),
+    "cv_subsample_mpeg2": (C.c_int, [C.POINTER(FrameF16), C.POINTER(Coded), C.c_void_p]),
     "cv_upload_display_table": (C.c_int, [C.c_float, C.POINTER(C.c_void_p)]),
     "cv_encode_u8": (C.c_int, [C.POINTER(FrameF16), C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "cv_to_argb32": (C.c_int, [C.POINTER(FrameF16), C.c_void_p, C.c_void_p]),

@@ -629,6 +629,118 @@ int cv_weave_fields_f16( rgba_frame_f16 *frame, const rgba_frame_f16 *even_rows,
                                         cudaMemcpyDeviceToDevice, cvi_stream( stream ) ), "cudaMemcpy2DAsync(weave)" );
 }
 
+/* ------------------------------------------------- colour transforms, crop */
+
+static int color_transform( rgba_frame_f16 *frame, const float m[9], int pre, int post, cv_stream stream, const char *who ) {
+    if( !frame ) return cvi_fail( CV_ERR_ARGUMENT, "%s: NULL frame", who );
+    CvDevice *dev = cvi_device();
+    if( !dev ) return CV_ERR_NOT_INITIALISED;
+    box2i cw;
+    box2i_intersect( &cw, &frame->current_window, &frame->full_window );
+    if( box2i_is_empty( &cw ) ) return CV_OK;
+    if( !frame->data ) return cvi_fail( CV_ERR_ARGUMENT, "%s: frame without data", who );
+
+    ColorArgs A;
+    memset( &A, 0, sizeof(A) );
+    A.frame = (uint2 *) frame->data; A.pitch = box_width( &frame->full_window );
+    A.ox = frame->full_window.min.x; A.oy = frame->full_window.min.y;
+    A.win = to_dev( &cw );
+    A.width = (uint32_t) box_width( &cw );
+    A.total = A.width * (uint32_t)( cw.max.y - cw.min.y + 1 );
+    A.magic = cvi_div_magic( A.width );
+    A.pre = pre >= 0 ? (const uint16_t *) dev->lut[pre] : NULL;
+    A.post = post >= 0 ? (const uint16_t *) dev->lut[post] : NULL;
+    memcpy( A.m, m, sizeof(A.m) );
+    return cvi_launch_color( &A, cvi_stream( stream ) );
+}
+
+int cv_color_rgb_to_xyz_sdtv( rgba_frame_f16 *frame, cv_stream stream ) {
+    /* color.c:111-114: columns r, g, b of the SMPTE-C RGB -> XYZ matrix, written here by output row */
+    static const float m[9] = { 0.3936f, 0.3652f, 0.1916f,   0.2124f, 0.7010f, 0.0865f,   0.0187f, 0.1119f, 0.9582f };
+    return color_transform( frame, m, CV_LUT_709_TO_LINEAR_SCENE, -1, stream, "cv_color_rgb_to_xyz_sdtv" );
+}
+
+int cv_color_xyz_to_srgb( rgba_frame_f16 *frame, cv_stream stream ) {
+    /* color.c:139-142 */
+    static const float m[9] = { 3.2410f, -1.5374f, -0.4986f,   -0.9692f, 1.8760f, 0.0416f,   0.0556f, -0.2040f, 1.0570f };
+    return color_transform( frame, m, -1, CV_LUT_LINEAR_TO_SRGB, stream, "cv_color_xyz_to_srgb" );
+}
+
+int cv_crop_f16( rgba_frame_f16 *frame, const box2i *crop_rect, cv_stream stream ) {
+    /* video_filter.c:79-95: pixels of the frame outside crop_rect become (0,0,0,0); the frame keeps its window.
+     * Up to four zero fills: the rows above and below the rectangle, the strips left and right of it. */
+    if( !frame || !crop_rect ) return cvi_fail( CV_ERR_ARGUMENT, "cv_crop_f16: NULL argument" );
+    if( !cvi_device() ) return CV_ERR_NOT_INITIALISED;
+    box2i cw, keep;
+    box2i_intersect( &cw, &frame->current_window, &frame->full_window );
+    if( box2i_is_empty( &cw ) ) return CV_OK;
+    if( !frame->data ) return cvi_fail( CV_ERR_ARGUMENT, "cv_crop_f16: frame without data" );
+    box2i_intersect( &keep, &cw, crop_rect );
+
+    box2i strips[4];
+    int count = 0;
+    if( box2i_is_empty( &keep ) )
+        strips[count++] = cw;
+    else {
+        if( keep.min.y > cw.min.y ) strips[count++] = (box2i) { { cw.min.x, cw.min.y }, { cw.max.x, keep.min.y - 1 } };
+        if( keep.max.y < cw.max.y ) strips[count++] = (box2i) { { cw.min.x, keep.max.y + 1 }, { cw.max.x, cw.max.y } };
+        if( keep.min.x > cw.min.x ) strips[count++] = (box2i) { { cw.min.x, keep.min.y }, { keep.min.x - 1, keep.max.y } };
+        if( keep.max.x < cw.max.x ) strips[count++] = (box2i) { { keep.max.x + 1, keep.min.y }, { cw.max.x, keep.max.y } };
+    }
+
+    for( int i = 0; i < count; i++ ) {
+        FillArgs A;
+        memset( &A, 0, sizeof(A) );
+        A.data = frame->data; A.pitch = box_width( &frame->full_window );
+        A.ox = frame->full_window.min.x; A.oy = frame->full_window.min.y; A.bytes = 8;
+        A.win = to_dev( &strips[i] );
+        A.width = (uint32_t) box_width( &strips[i] );
+        A.total = A.width * (uint32_t)( strips[i].max.y - strips[i].min.y + 1 );
+        A.magic = cvi_div_magic( A.width );
+        int rc = cvi_launch_fill( &A, cvi_stream( stream ) );
+        if( rc ) return rc;
+    }
+    return CV_OK;
+}
+
+/* ------------------------------------------------- MPEG-2 4:2:0 subsample */
+
+int cv_subsample_mpeg2( const rgba_frame_f16 *frame, const cv_coded *image, cv_stream stream ) {
+    if( !frame || !image ) return cvi_fail( CV_ERR_ARGUMENT, "cv_subsample_mpeg2: NULL argument" );
+    CvDevice *dev = cvi_device();
+    if( !dev ) return CV_ERR_NOT_INITIALISED;
+    if( image->layout != CV_LAYOUT_PLANAR )
+        return cvi_fail( CV_ERR_UNSUPPORTED, "cv_subsample_mpeg2: 4:2:0 is planar" );
+    if( image->width <= 0 || image->height <= 0 || (image->width & 1) || (image->height & 1) )
+        return cvi_fail( CV_ERR_ARGUMENT, "cv_subsample_mpeg2: picture %d x %d (both must be even and positive)", image->width, image->height );
+    if( image->matrix != CV_MATRIX_709 && image->matrix != CV_MATRIX_601 )
+        return cvi_fail( CV_ERR_ARGUMENT, "cv_subsample_mpeg2: matrix %d", image->matrix );
+    if( !image->plane[0] || !image->plane[1] || !image->plane[2] )
+        return cvi_fail( CV_ERR_ARGUMENT, "cv_subsample_mpeg2: NULL plane" );
+    if( image->stride[0] < image->width || image->stride[1] < image->width / 2 || image->stride[2] < image->width / 2 )
+        return cvi_fail( CV_ERR_ARGUMENT, "cv_subsample_mpeg2: stride shorter than the row" );
+
+    box2i cw;
+    box2i_intersect( &cw, &frame->current_window, &frame->full_window );
+    if( !box2i_is_empty( &cw ) && !frame->data )
+        return cvi_fail( CV_ERR_ARGUMENT, "cv_subsample_mpeg2: frame without data" );
+
+    Mpeg2Args A;
+    memset( &A, 0, sizeof(A) );
+    A.frame = (const uint2 *) frame->data; A.pitch = box_width( &frame->full_window );
+    A.ox = frame->full_window.min.x; A.oy = frame->full_window.min.y;
+    A.cw = to_dev( &cw );
+    A.pic_x = image->pic_x; A.pic_y = image->pic_y; A.width = image->width; A.height = image->height; A.matrix = image->matrix;
+    for( int i = 0; i < 3; i++ ) { A.plane[i] = image->plane[i]; A.stride[i] = image->stride[i]; }
+    A.to709 = dev->to709_f32;
+    A.luma_total = (uint32_t) image->width * (uint32_t) image->height;
+    A.luma_magic = cvi_div_magic( (uint32_t) image->width );
+    A.chroma_width = (uint32_t) image->width / 2;
+    A.chroma_total = A.chroma_width * ((uint32_t) image->height / 2);
+    A.chroma_magic = cvi_div_magic( A.chroma_width );
+    return cvi_launch_subsample_mpeg2( &A, cvi_stream( stream ) );
+}
+
 /* --------------------------------------------------- half arrays and tables */
 
 int cv_half_from_float( half *out, const float *in, size_t count, cv_stream stream ) {

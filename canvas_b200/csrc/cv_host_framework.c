@@ -523,6 +523,23 @@ void video_scale_bilinear_f32_pull( rgba_frame_f32 *target, v2f target_point, vi
     free( temp.data );
 }
 
+/* ------------------------------------------------------------------ colour transforms */
+
+static void color_in_place( rgba_frame_f16 *frame, int (*transform)( rgba_frame_f16 *, cv_stream ) ) {
+    /* color.c:100-160 work in place on current_window and have no way to report failure */
+    if( !frame || box2i_is_empty( &frame->current_window ) || !host_ready() ) return;
+    rgba_frame_f16 dev = { 0 };
+    const box2i keep = frame->current_window;
+    int rc = twin_f16( &dev, frame, 1 );
+    if( !rc ) rc = transform( &dev, NULL );
+    if( !rc ) rc = fetch_back_f16( frame, &dev );
+    frame->current_window = keep;
+    release_f16( &dev );
+}
+
+void video_color_rgb_to_xyz_sdtv( rgba_frame_f16 *frame ) { color_in_place( frame, cv_color_rgb_to_xyz_sdtv ); }
+void video_color_xyz_to_srgb( rgba_frame_f16 *frame )     { color_in_place( frame, cv_color_xyz_to_srgb ); }
+
 /* ------------------------------------------------------------------ DV conversion */
 
 enum { DV_WIDTH = 720, DV_HEIGHT = 480, DV_SUB_X = 4, DV_PIC_X = 0, DV_PIC_Y = -1 };

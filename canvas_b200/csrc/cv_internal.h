@@ -107,6 +107,20 @@ typedef struct ScaleArgs {
     const int32_t *start, *src; const float *coef;       /* per target line: taps start[t]..start[t+1]-1 */
 } ScaleArgs;
 
+typedef struct ColorArgs {
+    uint2 *frame; int32_t pitch, ox, oy; DevBox win; uint32_t width, total, magic;
+    const uint16_t *pre, *post;                             /* tables applied to all four channels before / after, or NULL */
+    float m[9];                                             /* out.x = (r*m[0] + g*m[1]) + b*m[2], ... */
+} ColorArgs;
+
+typedef struct Mpeg2Args {
+    const uint2 *frame; int32_t pitch, ox, oy; DevBox cw;   /* f16 source, valid pixels (others read as zero) */
+    int32_t pic_x, pic_y, width, height, matrix;            /* picture placement in frame coordinates, even width/height */
+    uint8_t *plane[3]; int32_t stride[3];
+    const float *to709;                                     /* half bits -> f32 linear->Rec.709, 65536 entries */
+    uint32_t luma_total, luma_magic, chroma_total, chroma_width, chroma_magic;
+} Mpeg2Args;
+
 enum { JOB_FLAG_SIMPLE = 1,     /* every layer covers the whole region, mix == 1, no bottom: no window tests */
        JOB_FLAG_EXACT = 2,      /* f32 frames involved: IEEE-division path only */
        JOB_FLAG_SEG = 4 };      /* every f16 input is pair-aligned with the output: the row-segment kernel (k_seg) applies */
@@ -127,6 +141,7 @@ typedef struct CvDevice {
     cudaStream_t stream;                /* library default stream */
     half *lut[CV_LUT_COUNT];            /* device copies, 65536 entries each */
     uint8_t *gamma45;                   /* device copy */
+    float *to709_f32;                   /* linear -> Rec.709 as f32 per half bit pattern (MPEG-2 subsample) */
     void *flush_buf; size_t flush_bytes;
     DevJob *job_ring_dev;               /* device ring for batched job descriptors */
     DevJob *job_ring_host;              /* pinned mirror */
@@ -164,6 +179,8 @@ int cvi_launch_over_f32( const OverF32Args *args, cudaStream_t stream );
 int cvi_launch_fill( const FillArgs *args, cudaStream_t stream );
 int cvi_launch_scale_axis( const ScaleArgs *args, cudaStream_t stream );
 int cvi_launch_gain_offset( const FillArgs *args, cudaStream_t stream );
+int cvi_launch_color( const ColorArgs *args, cudaStream_t stream );
+int cvi_launch_subsample_mpeg2( const Mpeg2Args *args, cudaStream_t stream );
 int cvi_kernels_init( void );                       /* per-device function attributes */
 uint32_t cvi_div_magic( uint32_t d );
 

@@ -23,6 +23,7 @@ static uint64_t g_launches;
 
 static half *g_host_lut[CV_LUT_COUNT];
 static uint8_t *g_host_gamma45;
+static float *g_host_to709_f32;
 static pthread_once_t g_tables_once = PTHREAD_ONCE_INIT;
 
 /* ------------------------------------------------------------------ errors */
@@ -111,6 +112,11 @@ static void build_tables( void ) {
         g_host_lut[which] = t;
     }
 
+    /* video_subsample.c:227-232, 258-263: the MPEG-2 shader's linear_to_rec709() on a half texel, kept in f32 */
+    g_host_to709_f32 = (float *) malloc( sizeof(float) * HALF_COUNT );
+    for( int i = 0; i < HALF_COUNT; i++ )
+        g_host_to709_f32[i] = tf_linear_to_709( host_h2f( (uint16_t) i ) );
+
     /* gammatab.c:8-38: truncating (uint8_t) of the clamped value; NaN clamps to 0 */
     g_host_gamma45 = (uint8_t *) malloc( HALF_COUNT );
     for( int i = 0; i < HALF_COUNT; i++ ) {
@@ -195,6 +201,8 @@ int cv_init( int device ) {
         }
         if( !rc ) rc = cvi_cuda( cudaMalloc( (void **) &dev->gamma45, HALF_COUNT ), "cudaMalloc(gamma45)" );
         if( !rc ) rc = cvi_cuda( cudaMemcpy( dev->gamma45, g_host_gamma45, HALF_COUNT, cudaMemcpyHostToDevice ), "cudaMemcpy(gamma45)" );
+        if( !rc ) rc = cvi_cuda( cudaMalloc( (void **) &dev->to709_f32, sizeof(float) * HALF_COUNT ), "cudaMalloc(to709_f32)" );
+        if( !rc ) rc = cvi_cuda( cudaMemcpy( dev->to709_f32, g_host_to709_f32, sizeof(float) * HALF_COUNT, cudaMemcpyHostToDevice ), "cudaMemcpy(to709_f32)" );
 
         if( !rc ) {
             dev->ready = 1;
@@ -229,6 +237,7 @@ void cv_shutdown( void ) {
         cvi_pool_release_all( d );
         for( int i = 0; i < CV_LUT_COUNT; i++ ) cudaFree( dev->lut[i] );
         cudaFree( dev->gamma45 );
+        cudaFree( dev->to709_f32 );
         cudaFree( dev->flush_buf );
         cudaFree( dev->job_ring_dev );
         cudaFreeHost( dev->job_ring_host );

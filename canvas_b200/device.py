@@ -266,6 +266,10 @@ def subsample_ycbcr8(frame, coded, stream=None):
     check(lib().cv_subsample_ycbcr8(C.byref(frame.c), C.byref(coded.c), stream), "cv_subsample_ycbcr8")
 
 
+def subsample_mpeg2(frame, coded, stream=None):
+    check(lib().cv_subsample_mpeg2(C.byref(frame.c), C.byref(coded.c), stream), "cv_subsample_mpeg2")
+
+
 def display_table(rendering_intent=1.25):
     p = C.c_void_p()
     check(lib().cv_upload_display_table(rendering_intent, C.byref(p)), "cv_upload_display_table")

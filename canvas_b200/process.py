@@ -698,6 +698,25 @@ class DVSubsampleFilter(CodedImageSource):
         return CodedImage([p.tobytes() for p in got], [720, 180, 180], [480, 480, 480])
 
 
+class MPEG2SubsampleFilter(CodedImageSource):
+    """Linear f16 RGBA -> planar 8-bit 4:2:0, Rec.601, 720 x 480, interlace-aware chroma (MPEG2SubsampleFilter.c:45-58,
+    video_subsample.c:212-290: GLSL in the reference, a CUDA kernel here)."""
+
+    _WINDOW = (0, 0, 719, 479)
+
+    def __init__(self, source):
+        self.source = source
+
+    def get_coded_image(self, frame):
+        out = dev.DeviceFrame16(self._WINDOW)
+        _run(self.source._describe(int(frame), self._WINDOW), self._WINDOW, out=out)
+        planes = [np.zeros((h, w), np.uint8) for w, h in ((720, 480), (360, 240), (360, 240))]
+        coded = dev.DeviceCoded(planes, 720, 480, sub_x=2, layout=_abi.CV_LAYOUT_PLANAR, matrix=_abi.CV_MATRIX_601, pic=(0, 0), zero=True)
+        dev.subsample_mpeg2(out, coded)
+        got = coded.download_planes()
+        return CodedImage([p.tobytes() for p in got], [720, 360, 360], [480, 240, 240])
+
+
 # ----------------------------------------------------------------------------- module functions
 
 class _Rational(C.Structure):

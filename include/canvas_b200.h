@@ -20,6 +20,8 @@
  *   cv_transfer          src/cprocess/gammatab.c:83-250 (video_transfer_*)
  *   cv_convert_ycbcr8    src/cprocess/video_reconstruct.c:50-137 (video_reconstruct_dv)
  *   cv_subsample_ycbcr8  src/cprocess/video_subsample.c:99-187 (video_subsample_dv)
+ *   cv_subsample_mpeg2   src/cprocess/video_subsample.c:212-290 (video_subsample_mpeg2_gl's shaders)
+ *   cv_color_*           src/cprocess/color.c:100-160 (video_color_rgb_to_xyz_sdtv, video_color_xyz_to_srgb)
  *   cv_copy_frame_f16    src/cprocess/video_mix.c:27-44
  *   cv_mix_cross_f16     src/cprocess/video_mix.c:46-71,107-235 pulled as f16 (main.c:44-72)
  *   cv_composite_over_f16 src/cprocess/workspace.c:494-550 + video_mix.c:237-370
@@ -198,6 +200,20 @@ int cv_gain_offset_f32( rgba_frame_f32 *frame, float gain, float offset, cv_stre
 /* The field weave of Pulldown23RemovalFilter (src/process/Pulldown23RemovalFilter.c:83-101): the even rows of
  * frame's current window are taken from `even_rows`. */
 int cv_weave_fields_f16( rgba_frame_f16 *frame, const rgba_frame_f16 *even_rows, cv_stream stream );
+
+/* video_color_rgb_to_xyz_sdtv / video_color_xyz_to_srgb (src/cprocess/color.c:100-131, :134-160), in place over
+ * current_window: [rec709->linear-scene table on all four channels,] 3x3 matrix in f32 on exact-widened halves,
+ * truncating pack [, linear->sRGB table on all four channels]. */
+int cv_color_rgb_to_xyz_sdtv( rgba_frame_f16 *frame, cv_stream stream );
+int cv_color_xyz_to_srgb( rgba_frame_f16 *frame, cv_stream stream );
+/* video_filter_crop_gl (src/cprocess/video_filter.c:79-95; GLSL only in the reference): pixels of current_window
+ * outside crop_rect become (0,0,0,0); the window itself is unchanged. */
+int cv_crop_f16( rgba_frame_f16 *frame, const box2i *crop_rect, cv_stream stream );
+/* video_subsample_mpeg2_gl (src/cprocess/video_subsample.c:212-290,314-520; GLSL only in the reference): linear f16
+ * RGBA -> planar 8-bit 4:2:0 (Y width x height, Cb/Cr width/2 x height/2), interlace-aware 6-tap chroma, the frame
+ * is NOT modified.  image: CV_LAYOUT_PLANAR, even width/height, pic_x/pic_y = frame coordinate of luma (0,0);
+ * sub_x is ignored.  The reference call is width 720, height 480, CV_MATRIX_601, picture at (0,0). */
+int cv_subsample_mpeg2( const rgba_frame_f16 *frame, const cv_coded *image, cv_stream stream );
 
 /* Display encode: target[px] = ramp[ sRGB[ frame[px] ] ] per channel (alpha too) over
  * frame->current_window; target is full_window-sized.  `u8_table` is a device copy of the

@@ -144,6 +144,9 @@ void video_mix_over_f32( rgba_frame_f32 *out, rgba_frame_f32 *b, float mix_b );
 /* video_scale.c:231-319 (reference framework.h:246-247) */
 void video_scale_bilinear_f32( rgba_frame_f32 *target, v2f target_point, rgba_frame_f32 *source, v2f source_point, v2f factors );
 void video_scale_bilinear_f32_pull( rgba_frame_f32 *target, v2f target_point, video_source *source, int frame, box2i *source_rect, v2f source_point, v2f factors );
+/* color.c:100-160: exported by the reference's library (EXPORT) without a declaration in its framework.h */
+void video_color_rgb_to_xyz_sdtv( rgba_frame_f16 *frame );
+void video_color_xyz_to_srgb( rgba_frame_f16 *frame );
 
 /* 65536-entry transfer tables applied as gathers; out may alias in. */
 void video_transfer_rec709_to_linear_scene( half *out, const half *in, size_t count );

@@ -397,6 +397,119 @@ void orc_subsample( orc_frame16 *frame, const orc_coded *im ) {
     free( temp_cr );
 }
 
+/* ---- MPEG-2 4:2:0 shaders restated: video_subsample.c:212-290 -------------------- */
+typedef struct { float y, pb, pr; } ypbpr;
+
+static ypbpr mpeg2_texel( const orc_frame16 *frame, const orc_coded *im, const float *to709, int px, int py ) {
+    /* GL_CLAMP_TO_EDGE on the picture, then the frame pixel the texel maps to (:404-405 input_offset) */
+    px = imin( imax( px, 0 ), im->width - 1 ) + im->pic_x;
+    py = imin( imax( py, 0 ), im->height - 1 ) + im->pic_y;
+    float r = 0.0f, g = 0.0f, b = 0.0f;
+    if( box_contains( &frame->current, px, py ) && box_contains( &frame->full, px, py ) ) {
+        const orc_px16 *p = px16( frame, px, py );
+        r = to709[p->r]; g = to709[p->g]; b = to709[p->b];      /* linear_to_rec709(), :227-232 */
+    }
+    const float (*m)[3] = rgb_to_ycbcr[im->matrix];             /* color * rgb2yuv, :235, :276-281 */
+    ypbpr out = {
+        (r * m[0][0] + g * m[0][1]) + b * m[0][2],
+        (r * m[1][0] + g * m[1][1]) + b * m[1][2],
+        (r * m[2][0] + g * m[2][1]) + b * m[2][2] };
+    return out;
+}
+
+static uint8_t unorm8( float v ) {
+    if( v != v ) return 0;
+    return (uint8_t) lrintf( clampf( v, 0.0f, 1.0f ) * 255.0f );
+}
+
+void orc_subsample_mpeg2( const orc_frame16 *frame, const orc_coded *im ) {
+    static float *to709 = NULL;
+    if( !to709 ) {
+        float *t = malloc( sizeof(float) * 65536 );
+        for( int i = 0; i < 65536; i++ )
+            t[i] = linear_to_rec709( orc_h2f( (uint16_t) i ) );
+        to709 = t;
+    }
+
+    const float ys = 219.0f / 255.0f, yo = 16.0f / 255.0f, cs = 224.0f / 255.0f, co = 128.0f / 255.0f;
+
+    /* luma shader, :234-239 */
+    for( int y = 0; y < im->height; y++ )
+        for( int x = 0; x < im->width; x++ )
+            im->plane[0][(size_t) y * im->stride[0] + x] = unorm8( mpeg2_texel( frame, im, to709, x, y ).y * ys + yo );
+
+    /* chroma shader, :265-286: luma_coord = 2 * chroma coordinate; near/far rows by the parity of the chroma row */
+    static const float weight[6] = { 3.0f / 16.0f, 6.0f / 16.0f, 3.0f / 16.0f, 1.0f / 16.0f, 2.0f / 16.0f, 1.0f / 16.0f };
+
+    for( int j = 0; j < im->height / 2; j++ ) {
+        const int odd = j & 1;
+        const int near_row = 2 * j + (odd ? 1 : 0), far_row = 2 * j + (odd ? -1 : 2);
+
+        for( int i = 0; i < im->width / 2; i++ ) {
+            float cb = 0.0f, cr = 0.0f;
+
+            for( int t = 0; t < 6; t++ ) {
+                const ypbpr v = mpeg2_texel( frame, im, to709, 2 * i + (t % 3) - 1, t < 3 ? near_row : far_row );
+                if( t == 0 ) { cb = weight[0] * v.pb; cr = weight[0] * v.pr; }
+                else { cb = cb + weight[t] * v.pb; cr = cr + weight[t] * v.pr; }
+            }
+
+            im->plane[1][(size_t) j * im->stride[1] + i] = unorm8( cb * cs + co );
+            im->plane[2][(size_t) j * im->stride[2] + i] = unorm8( cr * cs + co );
+        }
+    }
+}
+
+/* ---- color.c:100-160 -------------------------------------------------------------- */
+static void color_matrix( orc_frame16 *frame, const float a[3], const float b[3], const float c[3], int pre, int post ) {
+    static uint16_t *lut[4] = { NULL, NULL, NULL, NULL };
+    const int need[2] = { pre, post };
+    for( int i = 0; i < 2; i++ ) {
+        if( need[i] >= 0 && !lut[need[i]] ) {
+            uint16_t *t = malloc( sizeof(uint16_t) * 65536 );
+            orc_build_lut( need[i], t );
+            lut[need[i]] = t;
+        }
+    }
+
+    const orc_box box = box_intersect( &frame->current, &frame->full );
+
+    for( int y = box.min_y; y <= box.max_y; y++ ) {
+        for( int x = box.min_x; x <= box.max_x; x++ ) {
+            orc_px16 *h = px16( frame, x, y );
+            if( pre >= 0 ) { h->r = lut[pre][h->r]; h->g = lut[pre][h->g]; h->b = lut[pre][h->b]; h->a = lut[pre][h->a]; }
+
+            /* mult_mat_xyz (:35-43): a, b, c are the matrix COLUMNS */
+            const float r = orc_h2f( h->r ), g = orc_h2f( h->g ), bl = orc_h2f( h->b ), al = orc_h2f( h->a );
+            h->r = orc_f2h( r * a[0] + g * b[0] + bl * c[0] );
+            h->g = orc_f2h( r * a[1] + g * b[1] + bl * c[1] );
+            h->b = orc_f2h( r * a[2] + g * b[2] + bl * c[2] );
+            h->a = orc_f2h( al );
+
+            if( post >= 0 ) { h->r = lut[post][h->r]; h->g = lut[post][h->g]; h->b = lut[post][h->b]; h->a = lut[post][h->a]; }
+        }
+    }
+}
+
+void orc_color_rgb_to_xyz_sdtv( orc_frame16 *frame ) {
+    static const float r[3] = { 0.3936f, 0.2124f, 0.0187f }, g[3] = { 0.3652f, 0.7010f, 0.1119f }, b[3] = { 0.1916f, 0.0865f, 0.9582f };
+    color_matrix( frame, r, g, b, ORC_LUT_709_TO_LINEAR_SCENE, -1 );
+}
+
+void orc_color_xyz_to_srgb( orc_frame16 *frame ) {
+    static const float r[3] = { 3.2410f, -0.9692f, 0.0556f }, g[3] = { -1.5374f, 1.8760f, -0.2040f }, b[3] = { -0.4986f, 0.0416f, 1.0570f };
+    color_matrix( frame, r, g, b, -1, ORC_LUT_LINEAR_TO_SRGB );
+}
+
+/* ---- video_filter.c:79-95 (crop shader) -------------------------------------------- */
+void orc_crop_f16( orc_frame16 *frame, const orc_box *rect ) {
+    const orc_box box = box_intersect( &frame->current, &frame->full );
+    for( int y = box.min_y; y <= box.max_y; y++ )
+        for( int x = box.min_x; x <= box.max_x; x++ )
+            if( !box_contains( rect, x, y ) )
+                memset( px16( frame, x, y ), 0, sizeof(orc_px16) );
+}
+
 /* ---- copies: video_mix.c:27-44, 73-105 ----------------------------------------- */
 void orc_copy_frame_f16( orc_frame16 *out, const orc_frame16 *in ) {
     orc_box inner = box_intersect( &out->full, &in->current );

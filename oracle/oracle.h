@@ -77,6 +77,20 @@ void orc_reconstruct( orc_frame16 *frame, const orc_coded *image );
  * caller like coded_image_alloc0; mutates frame in place exactly like :147) */
 void orc_subsample( orc_frame16 *frame, const orc_coded *image );
 
+/* video_subsample.c:212-290 (GLSL in the reference -- PARITY UNPINNED: no CPU twin, no GL here): the MPEG-2 4:2:0
+ * shaders restated in C.  Choices the shader leaves to the GL implementation are fixed as: pow() = libm powf on the
+ * exact value of the half texel, dot products summed left to right, sin(y*3.14156) taken as its intended +-1,
+ * texels outside current_window are zero, coordinates clamp to the picture edge, a normalised byte is
+ * lrintf(clamp(v,0,1)*255) (NaN -> 0).  Planes: Y width x height, Cb/Cr width/2 x height/2.  frame is not modified. */
+void orc_subsample_mpeg2( const orc_frame16 *frame, const orc_coded *image );
+
+/* color.c:100-131, :134-160, in place over current_window */
+void orc_color_rgb_to_xyz_sdtv( orc_frame16 *frame );
+void orc_color_xyz_to_srgb( orc_frame16 *frame );
+
+/* video_filter.c:79-95 (GLSL only, parity unpinned): pixels of current_window outside rect become zero */
+void orc_crop_f16( orc_frame16 *frame, const orc_box *rect );
+
 /* video_mix.c:27-44, 73-105, 107-235, 237-370 */
 void orc_copy_frame_f16( orc_frame16 *out, const orc_frame16 *in );
 void orc_copy_frame_alpha_f32( orc_frame32 *out, const orc_frame32 *in, float alpha );

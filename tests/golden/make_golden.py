@@ -112,6 +112,13 @@ def main():
         out["scale_%d_fnv" % i] = np.uint32(O.fnv1a(dst.array))
         out["scale_%d_row" % i] = dst.array[dst.array.shape[0] // 2].view(np.uint32).copy()
 
+    # color.c:100-160 on a seeded frame with a partial window
+    for which in ("rgb_to_xyz_sdtv", "xyz_to_srgb"):
+        frame = O.synth_frame((-4, -2, 91, 53), 31, (0, 0, 80, 47))
+        getattr(L, "video_color_" + which)(C.byref(frame.c))
+        out["color_%s_fnv" % which] = np.uint32(O.fnv1a(frame.array))
+        out["color_%s_row" % which] = frame.array[20].copy()
+
     np.savez_compressed(os.path.join(HERE, "reference_vectors.npz"), **out)
     print("wrote %d arrays" % len(out))
 

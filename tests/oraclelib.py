@@ -195,6 +195,10 @@ def oracle():
         L.orc_mix_over_f32.argtypes = [C.POINTER(Frame32), C.POINTER(Frame32), C.c_float]
         L.orc_scale_bilinear_f32.argtypes = [C.POINTER(Frame32), C.c_float, C.c_float, C.POINTER(Frame32), C.c_float, C.c_float,
                                              C.c_float, C.c_float]
+        L.orc_subsample_mpeg2.argtypes = [C.POINTER(Frame16), C.POINTER(Coded)]
+        L.orc_color_rgb_to_xyz_sdtv.argtypes = [C.POINTER(Frame16)]
+        L.orc_color_xyz_to_srgb.argtypes = [C.POINTER(Frame16)]
+        L.orc_crop_f16.argtypes = [C.POINTER(Frame16), C.POINTER(Box)]
         L.orc_frame_f16_to_f32.argtypes = [C.POINTER(Frame32), C.POINTER(Frame16)]
         L.orc_frame_f32_to_f16.argtypes = [C.POINTER(Frame16), C.POINTER(Frame32)]
         L.orc_composite_f16.argtypes = [C.POINTER(Frame16), C.POINTER(Frame16), C.c_int]
@@ -239,6 +243,8 @@ class V2f(C.Structure):
 def _set_ref_types(L):
     L.video_scale_bilinear_f32.argtypes = [C.POINTER(Frame32), V2f, C.POINTER(Frame32), V2f, V2f]
     L.video_scale_bilinear_f32.restype = None
+    for name in ("video_color_rgb_to_xyz_sdtv", "video_color_xyz_to_srgb"):
+        getattr(L, name).argtypes, getattr(L, name).restype = [C.POINTER(Frame16)], None
     L.video_get_gamma45_ramp.restype = C.POINTER(C.c_uint8)
     for name in ("video_transfer_rec709_to_linear_scene", "video_transfer_rec709_to_linear_display",
                  "video_transfer_linear_to_rec709", "video_transfer_linear_to_sRGB"):

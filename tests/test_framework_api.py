@@ -82,7 +82,7 @@ def lib():
 FRAMEWORK_SYMBOLS = """init_half half_convert_from_float half_convert_to_float half_convert_from_float_fast
 half_convert_to_float_fast half_lookup get_frame_time get_time_frame gettime video_get_frame_f16 video_get_frame_f32
 video_copy_frame_f16 video_copy_frame_alpha_f32 video_mix_cross_f32_pull video_mix_cross_f32 video_mix_over_f32
-video_scale_bilinear_f32 video_scale_bilinear_f32_pull
+video_scale_bilinear_f32 video_scale_bilinear_f32_pull video_color_rgb_to_xyz_sdtv video_color_xyz_to_srgb
 video_transfer_rec709_to_linear_scene video_transfer_rec709_to_linear_display video_transfer_linear_to_rec709
 video_transfer_linear_to_sRGB video_get_gamma45_ramp coded_image_alloc coded_image_alloc0 video_reconstruct_dv
 video_subsample_dv workspace_create workspace_get_length workspace_add_item workspace_get_item workspace_remove_item
