@@ -305,7 +305,7 @@ def test_composite_large_random_stack_bit_exact(dev):
 
 # ------------------------------------------------------------------ same-signature batches (persistent k_seg)
 
-@pytest.mark.parametrize("shape", ["convert", "cross_u8", "timeline", "layers_u8"])
+@pytest.mark.parametrize("shape", ["convert", "cross_u8", "timeline", "layers_u8", "windows", "timeline_windows"])
 def test_uniform_batch_matches_oracle(dev, shape):
     """Runs of jobs with one signature go through ONE persistent launch (k_seg BATCH); every frame is
     checked against the oracle, and the launch count proves the batch form was taken."""
@@ -316,6 +316,10 @@ def test_uniform_batch_matches_oracle(dev, shape):
     pics_a = [O.synth_coded(w, h, 500 + i, 2, O.LAYOUT_UYVY, O.MATRIX_709, (0, 0), 0, True) for i in range(n)]
     pics_b = [O.synth_coded(w, h, 600 + i, 2, O.LAYOUT_UYVY, O.MATRIX_709, (0, 0), 0, True) for i in range(n)]
     frames = [O.synth_frame(full, 700 + i, full) for i in range(n + 3)]
+    # the same partial windows in every job (one geometry), odd edges included: the classifying mode, batched
+    boxes = [(0, 0, w - 1, h - 1), (13, 3, 150, 30), (64, 0, 199, 20), (1, 17, 77, 36)]
+    windowed = [[O.synth_frame(full, 900 + 10 * i + k, boxes[k]) for k in range(4)] for i in range(n)] if "windows" in shape else []
+    dev_w = [[to_device(dev, f) for f in row] for row in windowed]
     dev_a, dev_b = [device_coded(dev, p) for p in pics_a], [device_coded(dev, p) for p in pics_b]
     dev_f = [to_device(dev, f) for f in frames]
     table = dev.display_table(1.25)
@@ -342,6 +346,15 @@ def test_uniform_batch_matches_oracle(dev, shape):
             arr = (O.Frame16 * 3)(*[l.c for l in layers])
             orc.orc_timeline_frame_f16(C.byref(want.c), C.byref(pics_a[i].c), C.byref(pics_b[i].c), mix, arr, 3)
             job = dev.make_job(out=out, a=dev_a[i], b=dev_b[i], mix_b=mix, layers=[dev_f[i + 1], dev_f[i + 2], dev_f[i + 3]])
+        elif shape == "windows":
+            arr = (O.Frame16 * 4)(*[l.c for l in windowed[i]])
+            orc.orc_composite_f16(C.byref(want.c), arr, 4)
+            job = dev.make_job(out=out, layers=dev_w[i])
+        elif shape == "timeline_windows":
+            mix = 0.05 + 0.13 * i
+            arr = (O.Frame16 * 3)(*[l.c for l in windowed[i][1:]])
+            orc.orc_timeline_frame_f16(C.byref(want.c), C.byref(pics_a[i].c), C.byref(pics_b[i].c), mix, arr, 3)
+            job = dev.make_job(out=out, a=dev_a[i], b=dev_b[i], mix_b=mix, layers=dev_w[i][1:])
         else:
             layers = [frames[i], frames[i + 1], frames[i + 2]]
             arr = (O.Frame16 * 3)(*[l.c for l in layers])
@@ -358,7 +371,7 @@ def test_uniform_batch_matches_oracle(dev, shape):
     before = dev.lib().cv_kernel_launches()
     dev.render_frames(jobs)
     dev.sync()
-    if not os.environ.get("CV_SEG_NO_UNIFORM") and not os.environ.get("CV_NO_SEG_BATCH"):
+    if not os.environ.get("CV_NO_SEG_BATCH") and os.environ.get("CV_SEG_BATCH_GENERAL", "1") != "0":
         assert dev.lib().cv_kernel_launches() - before == 1, "the run was not taken as one batch launch"
     for i in range(n):
         assert_frames_equal(outs[i].download(), outs[i].current.tuple(), wants[i], "%s batch job %d" % (shape, i))
