@@ -140,6 +140,7 @@ typedef struct CvDevice {
     size_t l2_bytes;
     cudaStream_t stream;                /* library default stream */
     half *lut[CV_LUT_COUNT];            /* device copies, 65536 entries each */
+    half *lut709_compact;               /* rec709->linear restricted to the halves a conversion can produce (cv_runtime.c) */
     uint8_t *gamma45;                   /* device copy */
     float *to709_f32;                   /* linear -> Rec.709 as f32 per half bit pattern (MPEG-2 subsample) */
     void *flush_buf; size_t flush_bytes;

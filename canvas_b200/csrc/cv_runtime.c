@@ -24,6 +24,7 @@ static uint64_t g_launches;
 static half *g_host_lut[CV_LUT_COUNT];
 static uint8_t *g_host_gamma45;
 static float *g_host_to709_f32;
+static half *g_host_lut709_compact;
 static pthread_once_t g_tables_once = PTHREAD_ONCE_INIT;
 
 /* ------------------------------------------------------------------ errors */
@@ -111,6 +112,15 @@ static void build_tables( void ) {
         }
         g_host_lut[which] = t;
     }
+
+    /* The rec709->linear table restricted to what a Y'CbCr conversion can produce.  For any byte input and either
+     * matrix the converted value lies in (-1.14, 2.15) (extremes: B = y + 1.8556 cb at Y = 255/0, Cb = 255/0;
+     * tests/test_decode_tables.py walks the corners), so 0x4080 positive halves [0, 2.25) and 0x3F80 negative
+     * halves (-1.875, -0] suffice: 32768 entries.  Layout: entry h for a positive half, entry 0x7FFF - m for the
+     * negative half 0x8000 + m -- the index is h ^ 0xFFFF for negatives, one XOR with the replicated sign. */
+    g_host_lut709_compact = (half *) malloc( sizeof(half) * 32768 );
+    for( int i = 0; i < 32768; i++ )
+        g_host_lut709_compact[i] = g_host_lut[CV_LUT_709_TO_LINEAR_SCENE][i < 0x4080 ? i : 0x8000 + (0x7FFF - i)];
 
     /* video_subsample.c:227-232, 258-263: the MPEG-2 shader's linear_to_rec709() on a half texel, kept in f32 */
     g_host_to709_f32 = (float *) malloc( sizeof(float) * HALF_COUNT );
@@ -201,6 +211,8 @@ int cv_init( int device ) {
         }
         if( !rc ) rc = cvi_cuda( cudaMalloc( (void **) &dev->gamma45, HALF_COUNT ), "cudaMalloc(gamma45)" );
         if( !rc ) rc = cvi_cuda( cudaMemcpy( dev->gamma45, g_host_gamma45, HALF_COUNT, cudaMemcpyHostToDevice ), "cudaMemcpy(gamma45)" );
+        if( !rc ) rc = cvi_cuda( cudaMalloc( (void **) &dev->lut709_compact, sizeof(half) * 32768 ), "cudaMalloc(compact table)" );
+        if( !rc ) rc = cvi_cuda( cudaMemcpy( dev->lut709_compact, g_host_lut709_compact, sizeof(half) * 32768, cudaMemcpyHostToDevice ), "cudaMemcpy(compact table)" );
         if( !rc ) rc = cvi_cuda( cudaMalloc( (void **) &dev->to709_f32, sizeof(float) * HALF_COUNT ), "cudaMalloc(to709_f32)" );
         if( !rc ) rc = cvi_cuda( cudaMemcpy( dev->to709_f32, g_host_to709_f32, sizeof(float) * HALF_COUNT, cudaMemcpyHostToDevice ), "cudaMemcpy(to709_f32)" );
 
@@ -238,6 +250,7 @@ void cv_shutdown( void ) {
         for( int i = 0; i < CV_LUT_COUNT; i++ ) cudaFree( dev->lut[i] );
         cudaFree( dev->gamma45 );
         cudaFree( dev->to709_f32 );
+        cudaFree( dev->lut709_compact );
         cudaFree( dev->flush_buf );
         cudaFree( dev->job_ring_dev );
         cudaFreeHost( dev->job_ring_host );

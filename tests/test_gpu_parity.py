@@ -213,6 +213,39 @@ def test_timeline_frame_matches_oracle(dev, mix, layout):
     assert_frames_equal(out.download(), out.current.tuple(), want, "timeline mix=%r layout=%d" % (mix, layout))
 
 
+@pytest.mark.parametrize("matrix", [O.MATRIX_709, O.MATRIX_601])
+@pytest.mark.parametrize("layout", [O.LAYOUT_PLANAR, O.LAYOUT_UYVY, O.LAYOUT_YUY2])
+def test_corner_bytes_through_the_layered_kernels(dev, matrix, layout):
+    """Only bytes 0, 1, 254, 255 in every plane: the extremes of the converted range (past 2.0 and below -1.0), where the
+    64 KiB compact conversion table of the layered kernels ends.  Uniform and windowed forms, plus the bare conversion."""
+    w, h = 256, 24
+    full = (0, 0, w - 1, h - 1)
+    rng = np.random.default_rng(5 + matrix * 3 + layout)
+    pick = np.array([0, 1, 254, 255], np.uint8)
+    pic = O.CodedPicture(w, h, 2, layout, matrix, (0, 0))
+    pic.set_samples(pick[rng.integers(0, 4, (h, w))], pick[rng.integers(0, 4, (h, w // 2))], pick[rng.integers(0, 4, (h, w // 2))])
+    dpic = device_coded(dev, pic)
+
+    for boxes in ([full, full], [(20, 2, 201, 20), (0, 0, 99, 23)]):
+        overlays = [O.synth_frame(full, 61 + i, b) for i, b in enumerate(boxes)]
+        want = O.HostFrame16(full)
+        arr = (O.Frame16 * 2)(*[o.c for o in overlays])
+        O.oracle().orc_timeline_frame_f16(C.byref(want.c), C.byref(pic.c), None, 0.0, arr, 2)
+        out = poisoned(dev, full)
+        dev.render_frames([dev.make_job(out=out, a=dpic, layers=[to_device(dev, o) for o in overlays])])
+        dev.sync()
+        assert_frames_equal(out.download(), out.current.tuple(), want, "corner bytes under %r" % (boxes,))
+
+    want = O.HostFrame16(full)
+    O.oracle().orc_reconstruct(C.byref(want.c), C.byref(pic.c))
+    out = poisoned(dev, full)
+    dev.convert_ycbcr8(out, dpic)
+    dev.sync()
+    assert_frames_equal(out.download(), out.current.tuple(), want, "corner bytes, bare conversion")
+    values = want.array[..., :3].view(np.float16)
+    assert values.max() > 1.0 and values.min() < 0.0
+
+
 def test_render_frames_batch_equals_single(dev):
     """A batch (grid-walked jobs from device memory) gives the same pixels as one job per launch."""
     full = (0, 0, 95, 53)
