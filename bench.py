@@ -103,9 +103,18 @@ def synth_layer(rng, h, w):
     return a
 
 
+CONTENT = "noise"        # --content: "noise" = independent uniform bytes (the default; the worst case for the table gathers),
+                         #            "video" = smooth gradients + 2 LSB of noise, the spatial coherence of camera pictures
+
+
 def synth_uyvy(rng, h, w):
-    p = rng.integers(16, 236, size=(h, w * 2), dtype=np.uint8)
-    return p
+    if CONTENT == "noise":
+        return rng.integers(16, 236, size=(h, w * 2), dtype=np.uint8)
+    y, x = np.mgrid[0:h, 0:w * 2].astype(np.float32)
+    phase = rng.uniform(0, 6.28, 3)
+    p = 126 + 60 * np.sin(x / (w * 0.31) + phase[0]) + 40 * np.sin(y / (h * 0.23) + phase[1]) + 8 * np.sin((x + y) / 97.0 + phase[2])
+    p += rng.integers(-2, 3, size=p.shape)
+    return np.clip(p, 16, 235).astype(np.uint8)
 
 
 class ClockSampler(threading.Thread):
@@ -376,7 +385,7 @@ def run_ours(args):
         "metric": "f16 composite frames/sec (%s)" % name, "value": value, "unit": "frames/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f16 pixels, f32 arithmetic", "data": "synthetic",
+        "dtype": "f16 pixels, f32 arithmetic", "data": "synthetic" if CONTENT == "noise" else "synthetic (%s-like coded sources)" % CONTENT,
         "config": {"workload": name, "description": description, "width": w, "height": h,
                    "frames_per_step": FRAMES_PER_STEP, "input_sets": n_sets,
                    "l2": "inputs larger than L2 (%.0f MB per frame, %d rotating sets)" % (frame_bytes / 1e6, n_sets),
@@ -526,7 +535,7 @@ def run_reference(args):
         "impl": "reference", "metric": "f16 composite frames/sec (%s)" % name, "value": value, "unit": "frames/s",
         "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": steps, "warmup": min(args.warmup, 1),
         "ms_per_step": total_t / steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f16 pixels, f32 arithmetic", "data": "synthetic",
+        "dtype": "f16 pixels, f32 arithmetic", "data": "synthetic" if CONTENT == "noise" else "synthetic (%s-like coded sources)" % CONTENT,
         "config": {"workload": name, "description": description, "width": w, "height": h,
                    "frames_per_step": per_step, "note": "CPU reference arm: steps bounded to %d x %d frames" % (steps, per_step)},
         "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": kind,
@@ -545,8 +554,12 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="4k_8layer_composite", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--content", default="noise", choices=["noise", "video"],
+                    help="coded sources: independent random bytes (default) or smooth picture-like content")
     ap.add_argument("--no-batch", action="store_true", help="one launch per frame even for microsecond kernels")
     args = ap.parse_args()
+    global CONTENT
+    CONTENT = args.content
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
     if args.impl == "reference":
