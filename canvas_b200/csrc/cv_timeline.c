@@ -138,6 +138,8 @@ typedef struct Worker {
     cv_timeline_stats stats;
 } Worker;
 
+enum { CV_TIMELINE_GROUP = 16 };        /* frames per cv_render_frames() call of a GPU's worker */
+
 static double now_ms( void ) {
     struct timespec ts;
     clock_gettime( CLOCK_MONOTONIC, &ts );
@@ -151,6 +153,8 @@ static void *worker_main( void *arg ) {
     const cv_timeline_target *target = &run->targets[w->slot];
     cv_stream stream = NULL;
     cv_event begin = NULL, end = NULL, *slot_done = NULL;
+    cv_frame_job *jobs = NULL;
+    int64_t *frames = NULL;
     int rc;
 
     w->stats.device = device;
@@ -168,33 +172,49 @@ static void *worker_main( void *arg ) {
     const uint64_t launches0 = cv_kernel_launches();
     if( (rc = cv_event_record( begin, stream )) ) goto fail;
 
+    /* Frames are submitted in groups of up to `group` (one cv_render_frames() call: frames of one shape become ONE
+     * persistent launch, tables staged once); a group never holds more frames than the output ring has slots. */
+    int group = target->ring < CV_TIMELINE_GROUP ? target->ring : CV_TIMELINE_GROUP;
+    jobs = (cv_frame_job *) calloc( (size_t) group, sizeof(cv_frame_job) );
+    frames = (int64_t *) calloc( (size_t) group, sizeof(int64_t) );
+    if( !jobs || !frames ) { rc = cvi_fail( CV_ERR_MEMORY, "cv_timeline_render: out of host memory" ); goto fail; }
+
     int64_t produced = 0;
-    for( int64_t f = run->first; f <= run->last; f++ ) {
-        if( cv_timeline_device_of( f, run->first, run->chunk, run->n_gpus ) != w->slot )
-            continue;
+    int64_t f = run->first;
+    while( f <= run->last ) {
+        int n = 0;
+        for( ; f <= run->last && n < group; f++ ) {
+            if( cv_timeline_device_of( f, run->first, run->chunk, run->n_gpus ) != w->slot )
+                continue;
 
-        const int ring_slot = (int)( produced % target->ring );
-        if( produced >= target->ring )                      /* the sink's copies out of this slot have finished */
-            if( (rc = cv_event_sync( slot_done[ring_slot] )) ) goto fail;
+            const int ring_slot = (int)( (produced + n) % target->ring );
+            if( produced + n >= target->ring )              /* the sink's copies out of this slot have finished */
+                if( (rc = cv_event_sync( slot_done[ring_slot] )) ) goto fail;
 
-        cv_frame_job job;
-        memset( &job, 0, sizeof(job) );
-        rc = cv_timeline_job( run->items, run->item_count, w->slot, f, &job );
-        if( rc < 0 ) goto fail;
+            cv_frame_job *job = &jobs[n];
+            memset( job, 0, sizeof(*job) );
+            rc = cv_timeline_job( run->items, run->item_count, w->slot, f, job );
+            if( rc < 0 ) goto fail;
 
-        job.out = &target->out[ring_slot];
-        if( target->out_u8 ) {
-            job.out_u8 = target->out_u8[ring_slot];
-            job.u8_table = target->u8_table;
+            job->out = &target->out[ring_slot];
+            if( target->out_u8 ) {
+                job->out_u8 = target->out_u8[ring_slot];
+                job->u8_table = target->u8_table;
+            }
+            frames[n++] = f;
         }
-        if( (rc = cv_render_frames( &job, 1, stream )) ) goto fail;
+        if( n == 0 )
+            break;
+        if( (rc = cv_render_frames( jobs, n, stream )) ) goto fail;
 
-        if( run->sink ) {
-            rc = run->sink( run->user, w->slot, f, &job, stream );
-            if( rc ) { cvi_fail( rc, "cv_timeline_render: the sink failed at frame %lld", (long long) f ); goto fail; }
+        for( int i = 0; i < n; i++ ) {
+            if( run->sink ) {
+                rc = run->sink( run->user, w->slot, frames[i], &jobs[i], stream );
+                if( rc ) { cvi_fail( rc, "cv_timeline_render: the sink failed at frame %lld", (long long) frames[i] ); goto fail; }
+            }
+            if( (rc = cv_event_record( slot_done[(int)( (produced + i) % target->ring )], stream )) ) goto fail;
         }
-        if( (rc = cv_event_record( slot_done[ring_slot], stream )) ) goto fail;
-        produced++;
+        produced += n;
     }
 
     if( (rc = cv_event_record( end, stream )) ) goto fail;
@@ -219,6 +239,8 @@ fail:
             if( slot_done[i] ) cv_event_destroy( slot_done[i] );
         free( slot_done );
     }
+    free( jobs );
+    free( frames );
     if( begin ) cv_event_destroy( begin );
     if( end ) cv_event_destroy( end );
     if( stream ) cv_stream_destroy( stream );

@@ -67,6 +67,25 @@ class FrameFunction:
         return [tuple(self._values(float(f))) for f in frames]
 
 
+class FrameFuncPassThroughFilter(FrameFunction):
+    """FrameFuncPassThroughFilter(source, offset=0.0): the source's values at frame + offset; a constant source
+    (number, tuple, box) answers with the constant (FrameFuncPassThroughFilter.c:33-75)."""
+
+    def __init__(self, source, offset=0.0):
+        self.offset = float(offset)
+        self._holder = _Holder(source)
+        self._source = source
+
+    def source(self):
+        return self._source if self._holder.func is not None else None
+
+    def set_source(self, source):
+        self._holder, self._source = _Holder(source), source
+
+    def _values(self, frame):
+        return self._holder.values(frame + self.offset) if self._holder.func is not None else tuple(self._holder.constant)
+
+
 class LinearFrameFunc(FrameFunction):
     def __init__(self, a, b):
         self.a, self.b = float(np.float32(a)), float(np.float32(b))
@@ -715,6 +734,46 @@ class MPEG2SubsampleFilter(CodedImageSource):
         dev.subsample_mpeg2(out, coded)
         got = coded.download_planes()
         return CodedImage([p.tobytes() for p in got], [720, 360, 360], [480, 240, 240])
+
+
+class VideoPullQueueItem:
+    """The handle enqueue() returns; cancel() stops the callback (and the render, if it has not started)."""
+
+    def __init__(self):
+        self.active = True
+        self._future = None
+
+    def cancel(self):
+        self.active = False
+        if self._future is not None:
+            self._future.cancel()
+
+
+class VideoPullQueue:
+    """VideoPullQueue(): frames rendered ahead of need on two worker threads, `callback(frame_index, frame, user_data)`
+    when one is ready (VideoPullQueue.c:100-183).  The reference hands the callback to the glib main loop; there is no
+    main loop here, so it runs on the worker thread that rendered the frame."""
+
+    def __init__(self, device=None):
+        from concurrent.futures import ThreadPoolExecutor
+        self._device = dev.lib().cv_get_device() if device is None else int(device)
+        self._pool = ThreadPoolExecutor(max_workers=2, thread_name_prefix="VideoPullQueue")
+
+    def _work(self, item, source, frame_index, window, callback, user_data):
+        if not item.active:
+            return
+        check(dev.lib().cv_set_device(self._device), "cv_set_device")       # the library's device selection is per thread
+        frame = source.get_frame_f16(frame_index, window)
+        if item.active:
+            callback(frame_index, frame, user_data)
+
+    def enqueue(self, source, frame_index, window, callback, user_data):
+        item = VideoPullQueueItem()
+        item._future = self._pool.submit(self._work, item, source, int(frame_index), window, callback, user_data)
+        return item
+
+    def close(self):
+        self._pool.shutdown(wait=True)
 
 
 # ----------------------------------------------------------------------------- module functions

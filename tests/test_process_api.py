@@ -55,6 +55,23 @@ def test_lerp_func():
         process.LerpFunc((0,), (1,), 0)
 
 
+def test_frame_func_pass_through_filter():
+    """FrameFuncPassThroughFilter.c:33-75: values of the source at frame + offset; constants pass as they are"""
+    lerp = process.LerpFunc((0.0, 10.0, 0.0, 1.0), (4.0, 14.0, -4.0, 1.0), 4)
+    shifted = process.FrameFuncPassThroughFilter(lerp, 1.5)
+    assert shifted.source() is lerp
+    for frame in (0, 1, 2.25):
+        almost(shifted.get_values(frame)[0], lerp.get_values(frame + 1.5)[0])
+    almost(shifted.get_values([0, 2])[1], lerp.get_values(3.5)[0])
+    constant = process.FrameFuncPassThroughFilter((1.0, 2.0, 3.0, 4.0), 7.0)
+    assert constant.source() is None
+    almost(constant.get_values(5)[0], (1.0, 2.0, 3.0, 4.0))
+    constant.set_source(lerp)
+    almost(constant.get_values(0)[0], lerp.get_values(7.0)[0])
+    # a pass-through is itself a frame function: it can drive a source's colour
+    assert isinstance(shifted, process.FrameFunction)
+
+
 def test_animation_func_basic_and_move():
     func = process.AnimationFunc()
     func.add(process.AnimationPoint(process.POINT_HOLD, 0.0, 4.0))
@@ -322,3 +339,45 @@ def test_to_argb32_bytes_and_time_get_frame():
     O.oracle().orc_to_argb32(C.byref(f.c), O.ptr(ramp45), O.ptr(want))
     assert frame.to_argb32_bytes() == want.tobytes()
     assert process.time_get_frame(frame, 0, 5, box2i(*full)) > 0
+
+
+@pytest.mark.gpu
+def test_video_pull_queue():
+    """VideoPullQueue.c:100-183: frames rendered on worker threads, callback(frame_index, frame, user_data); cancel()"""
+    import threading
+    solid = process.SolidColorVideoSource(process.LerpFunc((0.0, 0.0, 0.0, 1.0), (8.0, 4.0, 2.0, 1.0), 8), box2i(0, 0, 15, 7))
+    queue = process.VideoPullQueue()
+    got, done = {}, threading.Event()
+
+    def callback(frame_index, frame, user_data):
+        got[frame_index] = (frame, user_data)
+        if len(got) == 8:
+            done.set()
+
+    items = [queue.enqueue(solid, i, box2i(-2, -2, 20, 10), callback, "tag%d" % i) for i in range(8)]
+    assert done.wait(60), sorted(got)
+    queue.close()
+    for i in range(8):
+        frame, tag = got[i]
+        assert tag == "tag%d" % i and frame.current_window == box2i(0, 0, 15, 7)
+        almost(frame.pixel(3, 3), rgba(float(i), i / 2.0, i / 4.0, 1.0))
+        assert frame.pixel(-1, -1) is None
+
+    # a cancelled item never calls back
+    queue = process.VideoPullQueue()
+    gate = threading.Event()
+
+    class Slow(process.VideoSource):
+        def _describe(self, frame_index, full):
+            gate.wait(30)
+            return solid._describe(frame_index, full)
+
+    calls = []
+    slow = Slow()
+    first = [queue.enqueue(slow, i, box2i(0, 0, 3, 3), lambda *a: calls.append(a[0]), None) for i in range(2)]    # both workers busy
+    late = queue.enqueue(slow, 9, box2i(0, 0, 3, 3), lambda *a: calls.append(a[0]), None)
+    late.cancel()
+    first[1].cancel()
+    gate.set()
+    queue.close()
+    assert calls == [0]
