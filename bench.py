@@ -16,8 +16,9 @@ Other workloads (explicit --workload only; parity-test configurations, not the b
     1080p_4layer_windows  4-layer workspace composite, layers 1-3 with partial windows (BASELINE.json configs[2];
                           bytes = 8 x (sum of layer window areas + output area) = 56.1 MB per frame)
 
-A "step" renders FRAMES_PER_STEP frames (one kernel launch per frame) from a ring of input sets, each
-larger than L2.  `value` is device-resident throughput (CUDA events on the launching stream);
+A "step" renders 16 (4K) or 120 (1080p) frames with ONE cv_render_frames() call -- frames of one shape become one
+persistent kernel launch; the plain 8-layer composite launches once per frame -- from a ring of input sets that
+together exceed L2 several times.  `value` is device-resident throughput (CUDA events on the launching stream);
 `e2e` moves every frame's inputs host->device from pinned memory and the result device->host
 inside the timed region.  Multi-GPU: frames are sharded by index over ranks (one process per
 GPU, no data-path collective; torch.distributed only provides the barrier and the max over ranks).
@@ -42,10 +43,11 @@ RING_BYTES = 400e6      # >= 3 x the 126 MB L2
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per FRAME, from the committed `ncu --set full` captures
-# (profiles/r1_kernels.md, profiles/r1_composite.md); None where no capture exists or a frame fits L2 under ncu's single launch
+# (profiles/r1_final.md)
 NCU_TRAFFIC_PER_FRAME = {
-    "4k_8layer_composite": 589.1e6, "4k_timeline": 4759e6 / 16, "4k_convert": 1267e6 / 16,
-    "4k_composite_convert": 8851e6 / 16, "1080p_cross_u8": 645e6 / 16,
+    "4k_8layer_composite": 589e6, "4k_timeline": 4881e6 / 16, "4k_convert": 1268e6 / 16, "4k_composite_convert": 8890e6 / 16,
+    "1080p_convert": 2460e6 / 120, "1080p_convert_planar": 2512e6 / 120, "1080p_cross_u8": 4958e6 / 120,
+    "1080p_4layer_windows": 6524e6 / 120,
 }
 
 
@@ -392,7 +394,7 @@ def run_ours(args):
                    "sharding": "frames by index, one process per GPU, no collective"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": (NCU_TRAFFIC_PER_FRAME[name] * frames_per_launch if name in NCU_TRAFFIC_PER_FRAME else None),
-                     "traffic_source": "profiles/r1_kernels.md (ncu --set full, per frame x frames per launch)",
+                     "traffic_source": "profiles/r1_final.md (ncu --set full, per frame x frames per launch)",
                      "peak_source": peak_source, "algorithmic_bytes_per_frame": frame_bytes,
                      "kernel_ms": kernel_ms},
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": sets[0].h2d_bytes * FRAMES_PER_STEP,
