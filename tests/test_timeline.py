@@ -178,7 +178,7 @@ def test_two_rank_plumbing_over_gloo(tmp_path):
 
 # ----------------------------------------------------------------------------- GPU
 
-def _timeline_on_gpus(lib, n_gpus):
+def _timeline_on_gpus(lib, n_gpus, ring=2, same_windows=False):
     from canvas_b200 import _abi as A
     from canvas_b200 import device as dev
     w, h = 192, 64
@@ -189,7 +189,7 @@ def _timeline_on_gpus(lib, n_gpus):
     pics_a = [O.synth_coded(w, h, 100 + i, 2, O.LAYOUT_UYVY, O.MATRIX_709) for i in range(3)]
     pics_b = [O.synth_coded(w, h, 200 + i, 2, O.LAYOUT_YUY2, O.MATRIX_601) for i in range(2)]
     over1 = [O.synth_frame(full, 300 + i, (16, 8, 150, 50)) for i in range(2)]
-    over2 = [O.synth_frame(full, 400 + i, (40 + 2 * i, 0, w - 1, h - 1)) for i in range(4)]
+    over2 = [O.synth_frame(full, 400 + i, (40 + (0 if same_windows else 2 * i), 0, w - 1, h - 1)) for i in range(4)]
 
     keep, clips = [], {}
     for name, hosts in (("a", pics_a), ("b", pics_b), ("o1", over1), ("o2", over2)):
@@ -218,7 +218,6 @@ def _timeline_on_gpus(lib, n_gpus):
     items[2].x, items[2].length, items[2].z, items[2].offset = 0, frames_total, 9, 3
     items[2].clips = clips["o2"]
 
-    ring = 2
     targets = (A.TimelineTarget * n_gpus)()
     outs = []
     for g in range(n_gpus):
@@ -247,7 +246,12 @@ def _timeline_on_gpus(lib, n_gpus):
     stats = (A.TimelineStats * n_gpus)()
     before = lib.cv_kernel_launches()
     dev.check(lib.cv_timeline_render(C.byref(run), stats), "cv_timeline_render")
-    assert lib.cv_kernel_launches() - before == frames_total
+    # one fused launch per frame, or fewer: consecutive frames of one shape on a GPU share a persistent launch
+    assert 0 < lib.cv_kernel_launches() - before <= frames_total
+    if same_windows and ring >= 4 and n_gpus == 1:
+        # frames 0 | 1-3 | 4-15 | 16-21 | 22 have one shape each (mix 0 and 1 short-circuit the crossfade): groups of `ring`
+        # frames, at most one extra launch per shape change
+        assert lib.cv_kernel_launches() - before <= (frames_total + ring - 1) // ring + 4
     assert sum(s.frames for s in stats) == frames_total
     assert [s.frames for s in stats] == [lib.cv_timeline_frames_of(g, 0, frames_total - 1, chunk, n_gpus) for g in range(n_gpus)]
     assert all(s.device_ms > 0 for s in stats if s.frames)
@@ -278,8 +282,15 @@ def test_timeline_render_one_gpu(lib):
 
 
 @pytest.mark.gpu
+def test_timeline_render_groups_frames_of_one_shape(lib):
+    """with a deep output ring the worker submits groups of frames; frames of one shape share a persistent launch"""
+    _timeline_on_gpus(lib, 1, ring=6, same_windows=True)
+
+
+@pytest.mark.gpu
 def test_timeline_render_all_gpus(lib):
     n = lib.cv_device_count()
     if n < 2:
         pytest.skip("one GPU visible")
     _timeline_on_gpus(lib, min(n, 8))
+    _timeline_on_gpus(lib, min(n, 8), ring=5, same_windows=True)
