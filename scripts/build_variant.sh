@@ -8,4 +8,5 @@ mkdir -p ../../variants build
     -I../../include -I/usr/local/cuda/include $flags -Xptxas -v -c cv_kernels.cu -o build/cv_kernels.$name.o 2> build/ptxas.$name.log
 objs=$(ls build/*.o | grep -v "cv_kernels")
 /usr/local/cuda/bin/nvcc -shared -o ../../variants/libcanvas_b200.$name.so $objs build/cv_kernels.$name.o -lpthread -lm
+rm -f build/cv_kernels.$name.o
 echo built variants/libcanvas_b200.$name.so
