@@ -303,7 +303,8 @@ int cv_timeline_job( const cv_timeline_item *items, int count, int slot, int64_t
 int cv_timeline_device_of( int64_t frame, int64_t first, int chunk, int n_gpus );
 int64_t cv_timeline_frames_of( int slot, int64_t first, int64_t last, int chunk, int n_gpus );
 
-/* Per-GPU outputs: a ring of device frames (and optionally 8-bit targets) reused round-robin. */
+/* Per-GPU outputs: a ring of device frames (and optionally 8-bit targets) reused round-robin; a deeper ring (8-16)
+ * lets more frames share a launch. */
 typedef struct {
     rgba_frame_f16 *out;            /* [ring] device frames from cv_frame_alloc_f16 on that GPU */
     rgba_u8 **out_u8;               /* [ring] device buffers or NULL */
@@ -312,9 +313,11 @@ typedef struct {
     int32_t reserved;
 } cv_timeline_target;
 
-/* Called on the GPU's own host thread right after frame `frame` was enqueued on `stream`; it may
- * enqueue copies out of job->out / job->out_u8 on the same stream (the ring slot is not reused before
- * they finish).  Frames of one GPU arrive in ascending order; different GPUs call concurrently. */
+/* Called on the GPU's own host thread after frame `frame` was enqueued on `stream` (frames are enqueued in groups
+ * of up to min(ring, 16): frames of one shape share one persistent launch; the sink is called once per frame when
+ * its group has been enqueued); it may enqueue copies out of job->out / job->out_u8 on the same stream (the ring
+ * slot is not reused before they finish).  Frames of one GPU arrive in ascending order; different GPUs call
+ * concurrently. */
 typedef int (*cv_timeline_sink)( void *user, int slot, int64_t frame, const cv_frame_job *job, cv_stream stream );
 
 typedef struct {
