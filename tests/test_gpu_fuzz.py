@@ -105,3 +105,35 @@ def test_random_frame_program(dev, seed):
     what = "seed %d: %dx%d at (%d,%d), bottom %s, %d layers, %d job(s)" % (seed, w, h, ox, oy, bottom, n_layers, n_jobs)
     for j in range(n_jobs):
         assert_frames_equal(outs[j].download(), outs[j].current.tuple(), wants[j], "%s, job %d" % (what, j))
+
+
+@pytest.mark.parametrize("seed", range(max(8, CASES // 4)))
+def test_random_full_window_stack(dev, seed):
+    """the TMA-ring composite (every layer covers the frame): random sizes up to a few thousand pixels wide, so that the
+    warps' row cursors wrap in every way; optional 8-bit output sends the same stack through the row-segment kernel"""
+    rng = np.random.default_rng(5000 + seed)
+    orc = O.oracle()
+    w = 2 * int(rng.integers(17, 2100)) if rng.random() < 0.5 else 2 * int(rng.integers(17, 200))
+    h = int(rng.integers(1, 40)) if w > 600 else int(rng.integers(1, 300))
+    ox, oy = 2 * int(rng.integers(-3, 4)), int(rng.integers(-3, 4))
+    full = (ox, oy, ox + w - 1, oy + h - 1)
+    n = int(rng.integers(1, 9))
+    layers = [O.synth_frame(full, 7000 + 16 * seed + k) for k in range(n)]
+    want = O.HostFrame16(full)
+    arr = (O.Frame16 * n)(*[l.c for l in layers])
+    orc.orc_composite_f16(C.byref(want.c), arr, n)
+    out = poisoned(dev, full)
+    dl = [to_device(dev, l) for l in layers]
+    u8 = table = None
+    if rng.random() < 0.3:
+        u8, table = dev.DeviceBuffer(w * h * 4), dev.display_table(1.25)
+    dev.render_frames([dev.make_job(out=out, layers=dl, out_u8=u8, u8_table=table)])
+    dev.sync()
+    assert_frames_equal(out.download(), out.current.tuple(), want, "seed %d: %d layers %dx%d" % (seed, n, w, h))
+    if u8 is not None:
+        srgb, ramp = np.zeros(65536, np.uint16), np.zeros(65536, np.uint8)
+        orc.orc_build_lut(O.LUT_LINEAR_TO_SRGB, O.ptr(srgb))
+        orc.orc_build_intent_ramp(1.25, O.ptr(ramp))
+        target = np.zeros((h, w, 4), np.uint8)
+        orc.orc_encode_u8(C.byref(want.c), O.ptr(srgb), O.ptr(ramp), O.ptr(target))
+        assert np.array_equal(u8.download(np.uint8, (h, w, 4)), target), "seed %d: 8-bit output" % seed
