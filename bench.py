@@ -105,6 +105,7 @@ def synth_layer(rng, h, w):
     return a
 
 
+PLANAR = False
 CONTENT = "noise"        # --content: "noise" = independent uniform bytes (the default; the worst case for the table gathers),
                          #            "video" = smooth gradients + 2 LSB of noise, the spatial coherence of camera pictures
 
@@ -187,6 +188,7 @@ class InputSet:
             self.uploads.append((frame.c.data, pinned))
 
         def add_coded(i, planar=False):
+            planar = planar or PLANAR           # --planar: every coded source as three planes (the reference's coded_image layout)
             arr = np.roll(base["uyvy"][i % len(base["uyvy"])], 4 * (len(self.coded) + 1), axis=1)
             if planar:          # the same samples as three planes: UYVY = Cb Y0 Cr Y1
                 planes = [np.ascontiguousarray(arr[:, 1::2]), np.ascontiguousarray(arr[:, 0::4]), np.ascontiguousarray(arr[:, 2::4])]
@@ -387,7 +389,7 @@ def run_ours(args):
         "metric": "f16 composite frames/sec (%s)" % name, "value": value, "unit": "frames/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f16 pixels, f32 arithmetic", "data": "synthetic" if CONTENT == "noise" else "synthetic (%s-like coded sources)" % CONTENT,
+        "dtype": "f16 pixels, f32 arithmetic", "data": ("synthetic" if CONTENT == "noise" else "synthetic (%s-like coded sources)" % CONTENT) + (", planar 4:2:2" if PLANAR else ""),
         "config": {"workload": name, "description": description, "width": w, "height": h,
                    "frames_per_step": FRAMES_PER_STEP, "input_sets": n_sets,
                    "l2": "inputs larger than L2 (%.0f MB per frame, %d rotating sets)" % (frame_bytes / 1e6, n_sets),
@@ -537,7 +539,7 @@ def run_reference(args):
         "impl": "reference", "metric": "f16 composite frames/sec (%s)" % name, "value": value, "unit": "frames/s",
         "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": steps, "warmup": min(args.warmup, 1),
         "ms_per_step": total_t / steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f16 pixels, f32 arithmetic", "data": "synthetic" if CONTENT == "noise" else "synthetic (%s-like coded sources)" % CONTENT,
+        "dtype": "f16 pixels, f32 arithmetic", "data": ("synthetic" if CONTENT == "noise" else "synthetic (%s-like coded sources)" % CONTENT) + (", planar 4:2:2" if PLANAR else ""),
         "config": {"workload": name, "description": description, "width": w, "height": h,
                    "frames_per_step": per_step, "note": "CPU reference arm: steps bounded to %d x %d frames" % (steps, per_step)},
         "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": kind,
@@ -556,12 +558,13 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="4k_8layer_composite", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--planar", action="store_true", help="4:2:2 sources as three planes instead of packed UYVY")
     ap.add_argument("--content", default="noise", choices=["noise", "video"],
                     help="coded sources: independent random bytes (default) or smooth picture-like content")
     ap.add_argument("--no-batch", action="store_true", help="one launch per frame even for microsecond kernels")
     args = ap.parse_args()
-    global CONTENT
-    CONTENT = args.content
+    global CONTENT, PLANAR
+    CONTENT, PLANAR = args.content, args.planar
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
     if args.impl == "reference":
