@@ -43,11 +43,11 @@ RING_BYTES = 400e6      # >= 3 x the 126 MB L2
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per FRAME, from the committed `ncu --set full` captures
-# (profiles/r1_final.md)
+# (profiles/r1_final.md; the windows workload from profiles/r1_general.md)
 NCU_TRAFFIC_PER_FRAME = {
     "4k_8layer_composite": 588e6, "4k_timeline": 4881e6 / 16, "4k_convert": 1268e6 / 16, "4k_composite_convert": 8893e6 / 16,
     "1080p_convert": 2460e6 / 120, "1080p_convert_planar": 2512e6 / 120, "1080p_cross_u8": 4958e6 / 120,
-    "1080p_4layer_windows": 6524e6 / 120,
+    "1080p_4layer_windows": 6412e6 / 120,
 }
 
 
