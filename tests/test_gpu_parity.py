@@ -80,6 +80,13 @@ COMPOSITE_CASES = {
                                       ((0, 0, 31, 31), (8, 1, 30, 12))]),
     "odd_width": ((0, 0, 44, 20), [((0, 0, 44, 20), (0, 0, 44, 20)), ((0, 0, 44, 20), (7, 3, 33, 18))]),
     "sixteen": ((0, 0, 63, 31), [((0, 0, 63, 31), (i, i % 5, 63 - i, 31 - (i % 3))) for i in range(16)]),
+    # rows of several 192-pixel (3 pairs per lane) / 128-pixel segments: window edges inside, on and next to segment
+    # boundaries; five ring slots take the 3-pair window-classifying kernels, nine the 2-pair ones
+    "wide_windows_5": ((0, 0, 1001, 11), [((0, 0, 1001, 11), (0, 0, 1001, 11)), ((0, 0, 1001, 11), (191, 1, 576, 9)),
+                                          ((0, 0, 1001, 11), (192, 0, 383, 11)), ((-6, -2, 1100, 14), (385, 3, 1001, 7)),
+                                          ((0, 0, 1001, 11), (7, 2, 130, 10))]),
+    "wide_windows_9": ((-2, 0, 899, 8), [((-2, 0, 899, 8), (-2, 0, 899, 8))] +
+                                        [((-2, 0, 899, 8), (-2 + 97 * i, i % 3, 899 - 61 * i, 8 - (i % 2))) for i in range(1, 9)]),
 }
 
 
