@@ -4,24 +4,29 @@ reference CPU path timed beside it.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
 
-Default workload (BASELINE.json: the configuration the metric is quoted on):
+Headline workload (BASELINE.json: the configuration the metric is quoted on):
     4k_8layer_composite   3840x2160, 8 full-window f16 RGBA layers composited "over" -> f16 out,
                           72 algorithmic bytes per pixel = 597.2 MB per frame.
-Other workloads (explicit --workload only; parity-test configurations, not the bench line):
+The other BASELINE.json configurations are measured in the same run (each about 0.3 s of device time) and
+reported in the line's `other_workloads` array; `--workload NAME` makes any of them the headline instead:
     4k_composite_convert  bottom layer is an 8-bit 4:2:2 picture converted in-kernel + 7 f16 layers (66 B/px)
     4k_convert            4:2:2 Rec.709 -> linear f16 RGBA (10 B/px)
     1080p_convert         same at 1920x1080 (BASELINE.json configs[0]); 1080p_convert_planar: Y, Cb, Cr planes
-    1080p_cross_u8        two f16 sources crossfaded, display-encoded to 8-bit (20 B/px)
-    4k_timeline           2 x (4:2:2 -> f16) -> crossfade -> + 3 overlays -> f16 (36 B/px at full coverage)
-    1080p_4layer_windows  4-layer workspace composite, layers 1-3 with partial windows (BASELINE.json configs[2];
+    1080p_cross_u8        two f16 sources crossfaded, display-encoded to 8-bit (20 B/px; configs[1])
+    1080p_4layer_windows  4-layer workspace composite, layers 1-3 with partial windows (configs[2];
                           bytes = 8 x (sum of layer window areas + output area) = 56.1 MB per frame)
+    4k_timeline           2 x (4:2:2 -> f16) -> crossfade -> + 3 full-window overlays -> f16 (36 B/px)
+    4k_timeline_windows   the same with PARTIAL overlay windows (configs[4]'s frame; 28.6 B/px)
 
-A "step" renders 16 (4K) or 120 (1080p) frames with ONE cv_render_frames() call -- frames of one shape become one
-persistent kernel launch; the plain 8-layer composite launches once per frame -- from a ring of input sets that
-together exceed L2 several times.  `value` is device-resident throughput (CUDA events on the launching stream);
-`e2e` moves every frame's inputs host->device from pinned memory and the result device->host
-inside the timed region.  Multi-GPU: frames are sharded by index over ranks (one process per
-GPU, no data-path collective; torch.distributed only provides the barrier and the max over ranks).
+A "step" renders enough frames to last about 50 ms (512 frames at 4K for the headline) with ONE
+cv_render_frames() call -- frames of one shape become persistent kernel launches of up to 256 frames; the plain
+8-layer composite launches once per frame -- from a ring of input sets that together exceed L2 several times.
+`value` is device-resident throughput (CUDA events on the launching stream); `e2e` moves every frame's inputs
+host->device from pinned memory and the result device->host inside the timed region.  After the timed region the
+outputs the timed launches wrote are compared with the oracle (`parity_checked`, `max_ulp`).
+Multi-GPU: frames are sharded by index over ranks (one process per GPU, no data-path collective;
+torch.distributed only provides the barrier and the max over ranks); `scheduler` is the same timeline rendered by
+ONE cv_timeline_render() call over all GPUs (rank 0, while the other ranks idle).
 """
 import argparse
 import ctypes as C
@@ -37,23 +42,33 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-FRAMES_PER_STEP = 16
 INPUT_SETS = 3          # at least; small frames get more so that the ring of sets stays larger than L2
 RING_BYTES = 400e6      # >= 3 x the 126 MB L2
+STEP_MS = 50.0          # a step lasts about this long, so that 20 steps are a second of sustained load
 
-
-# dram__bytes_read.sum + dram__bytes_write.sum per FRAME, from the committed `ncu --set full` captures
-# (profiles/r1_final.md; the windows workload from profiles/r1_general.md)
-NCU_TRAFFIC_PER_FRAME = {
-    "4k_8layer_composite": 588e6, "4k_timeline": 4881e6 / 16, "4k_convert": 1268e6 / 16, "4k_composite_convert": 8893e6 / 16,
-    "1080p_convert": 2460e6 / 120, "1080p_convert_planar": 2512e6 / 120, "1080p_cross_u8": 4958e6 / 120,
-    "1080p_4layer_windows": 6412e6 / 120,
+WORKLOADS = {
+    # name: (width, height, bytes per pixel, frames per step (about STEP_MS of device time), description)
+    "4k_8layer_composite": (3840, 2160, 72, 512, "3840x2160 8-layer f16 alpha-over workspace composite -> f16"),
+    "4k_composite_convert": (3840, 2160, 66, 448, "3840x2160 4:2:2 bottom converted in-kernel + 7 f16 layers -> f16"),
+    "4k_convert": (3840, 2160, 10, 3072, "3840x2160 8-bit 4:2:2 Rec.709 -> linear f16 RGBA"),
+    "1080p_convert": (1920, 1080, 10, 12000, "1920x1080 8-bit 4:2:2 Rec.709 -> linear f16 RGBA"),
+    "1080p_convert_planar": (1920, 1080, 10, 9600, "1920x1080 8-bit planar 4:2:2 Rec.709 (Y, Cb, Cr planes) -> linear f16 RGBA"),
+    "1080p_cross_u8": (1920, 1080, 20, 6000, "1920x1080 two-source f16 crossfade -> 8-bit display encode"),
+    "4k_timeline": (3840, 2160, 36, 640, "3840x2160 2x(4:2:2->f16) crossfade + 3 f16 overlays -> f16"),
+    "4k_timeline_windows": (3840, 2160, None, 512, "3840x2160 2x(4:2:2->f16) crossfade + 3 f16 overlays with partial windows -> f16"),
+    "1080p_4layer_windows": (1920, 1080, None, 3840, "1920x1080 4-layer alpha-over workspace composite, partial layer windows -> f16"),
 }
+# what the driver-run line reports next to the headline: BASELINE.json configs[0..4] and their variants
+OTHER_WORKLOADS = ["1080p_convert", "1080p_convert_planar", "1080p_cross_u8", "1080p_4layer_windows", "4k_composite_convert",
+                   "4k_convert", "4k_timeline", "4k_timeline_windows"]
+
+# layer windows of 1080p_4layer_windows (layer 0 covers the frame); inclusive corners
+WINDOWS_1080P = [(0, 0, 1919, 1079), (200, 100, 1719, 979), (480, 0, 1919, 700), (0, 540, 959, 1079)]
 
 
-def frames_per_step(workload):
-    """4K: 16 frames a step; 1080p: 120 (BASELINE.json configs[0] is quoted on 120 frames), so that a step is a few ms"""
-    return FRAMES_PER_STEP if workload.startswith("4k") else 120
+def timeline_windows(w, h):
+    """Overlay windows of the configs[4] timeline frame (the same boxes scripts/bench_scheduler.py uses)."""
+    return [(w // 8, h // 8, w - 1, h - 1), (0, 0, 3 * w // 4 - 1, h - 1), (w // 4, 0, w - 1, 3 * h // 4 - 1)]
 
 
 def load_peaks():
@@ -65,33 +80,28 @@ def load_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-WORKLOADS = {
-    # name: (width, height, bytes per pixel, description)
-    "4k_8layer_composite": (3840, 2160, 72, "3840x2160 8-layer f16 alpha-over workspace composite -> f16"),
-    "4k_composite_convert": (3840, 2160, 66, "3840x2160 4:2:2 bottom converted in-kernel + 7 f16 layers -> f16"),
-    "4k_convert": (3840, 2160, 10, "3840x2160 8-bit 4:2:2 Rec.709 -> linear f16 RGBA"),
-    "1080p_convert": (1920, 1080, 10, "1920x1080 8-bit 4:2:2 Rec.709 -> linear f16 RGBA"),
-    "1080p_convert_planar": (1920, 1080, 10, "1920x1080 8-bit planar 4:2:2 Rec.709 (Y, Cb, Cr planes) -> linear f16 RGBA"),
-    "1080p_cross_u8": (1920, 1080, 20, "1920x1080 two-source f16 crossfade -> 8-bit display encode"),
-    "4k_timeline": (3840, 2160, 36, "3840x2160 2x(4:2:2->f16) crossfade + 3 f16 overlays -> f16"),
-    "1080p_4layer_windows": (1920, 1080, None, "1920x1080 4-layer alpha-over workspace composite, partial layer windows -> f16"),
-}
-
-
-# ----------------------------------------------------------------------------- synthetic inputs
-
-# layer windows of 1080p_4layer_windows (layer 0 covers the frame); inclusive corners
-WINDOWS_1080P = [(0, 0, 1919, 1079), (200, 100, 1719, 979), (480, 0, 1919, 700), (0, 540, 959, 1079)]
+def load_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per FRAME by workload, written by scripts/ncu_summary.py from
+    the committed `ncu --set full` captures (profiles/traffic.json)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
 
 
 def workload_bytes(name):
     """Algorithmic bytes per frame: every input pixel read once, every output pixel written once."""
-    w, h, per_px, _ = WORKLOADS[name]
+    w, h, per_px = WORKLOADS[name][:3]
     if per_px is not None:
         return w * h * per_px
     area = lambda b: (b[2] - b[0] + 1) * (b[3] - b[1] + 1)
+    if name == "4k_timeline_windows":
+        return 4 * w * h + 8 * (sum(area(b) for b in timeline_windows(w, h)) + w * h)
     return 8 * (sum(area(b) for b in WINDOWS_1080P) + w * h)
 
+
+# ----------------------------------------------------------------------------- synthetic inputs
 
 def synth_layer(rng, h, w):
     """Raw half bits: rgb uniform halves in [0,1], alpha from {0,1/4,1/2,3/4,1,1} or a random fraction."""
@@ -140,7 +150,7 @@ class ClockSampler(threading.Thread):
                     self.samples.append(parts)
             except Exception:
                 pass
-            self.stop_flag.wait(0.2)
+            self.stop_flag.wait(0.1)
 
     def finish(self):
         self.stop_flag.set()
@@ -151,6 +161,42 @@ class ClockSampler(threading.Thread):
         reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v.lower().startswith("active")})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": reasons, "samples": len(self.samples)}
+
+
+# ----------------------------------------------------------------------------- NUMA placement
+
+def gpu_numa_cpus(local_gpu):
+    """The CPUs of the NUMA node the GPU's PCIe root hangs off (None when the box does not say)."""
+    try:
+        out = subprocess.run(["nvidia-smi", "-i", str(local_gpu), "--query-gpu=pci.bus_id", "--format=csv,noheader"],
+                             capture_output=True, text=True, timeout=10).stdout.strip().lower()
+        if not out:
+            return None
+        bus = out[-12:] if len(out) > 12 else out          # 00000000:1B:00.0 -> 0000:1b:00.0
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bus).read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        usable = cpus & set(os.sched_getaffinity(0))
+        return (node, sorted(usable)) if usable else None
+    except Exception:
+        return None
+
+
+def pin_to_gpu_node(local_gpu):
+    """Runs this process on the GPU's NUMA node, so that pinned staging memory is first-touched there."""
+    found = gpu_numa_cpus(local_gpu)
+    if not found:
+        return None
+    node, cpus = found
+    try:
+        os.sched_setaffinity(0, cpus)
+        return {"node": node, "cpus": len(cpus)}
+    except Exception:
+        return None
 
 
 # ----------------------------------------------------------------------------- our arm
@@ -166,41 +212,54 @@ class PinnedArray:
         buf = (C.c_uint8 * self.nbytes).from_address(self.ptr.value)
         self.array = np.frombuffer(buf, dtype=dtype).reshape(shape)
 
+    def free(self):
+        if self.ptr:
+            self.array = None
+            self.dev.lib().cv_free(self.ptr, 1)
+            self.ptr = C.c_void_p()
+
 
 class InputSet:
-    """Device-resident inputs + output of one frame, with pinned host mirrors for the e2e leg."""
+    """Device-resident inputs + output of one frame, pinned host mirrors for the e2e leg and the host copies the
+    oracle check reads (`host_layers`: (array, window); `host_coded`: (UYVY rows, planar?))."""
 
-    def __init__(self, dev, name, rng, base):
-        w, h, _, _ = WORKLOADS[name]
+    def __init__(self, dev, name, base, pinned=True):
+        w, h = WORKLOADS[name][:2]
         full = (0, 0, w - 1, h - 1)
-        self.dev, self.full = dev, full
-        self.layers, self.coded, self.host, self.uploads = [], [], [], []
+        self.dev, self.full, self.name = dev, full, name
+        self.layers, self.coded, self.uploads = [], [], []
+        self.host_layers, self.host_coded = [], []
         self.out = dev.DeviceFrame16(full)
         self.out_u8 = None
+        self.mix_b = 0.375
         self.d2h_bytes = w * h * 8
+
+        def mirror(dst, arr, dtype):
+            if pinned:
+                p = PinnedArray(dev, arr.shape, dtype)
+                p.array[...] = arr
+                self.uploads.append((dst, p))
 
         def add_layer(i, window=None):
             arr = np.roll(base["layer"][i % len(base["layer"])], 17 * len(self.layers) + 1, axis=1)
             frame = dev.DeviceFrame16.from_numpy(arr, full, window)
-            pinned = PinnedArray(dev, arr.shape, np.uint16)
-            pinned.array[...] = arr
             self.layers.append(frame)
-            self.uploads.append((frame.c.data, pinned))
+            self.host_layers.append((arr, window or full))
+            mirror(frame.c.data, arr, np.uint16)
 
         def add_coded(i, planar=False):
             planar = planar or PLANAR           # --planar: every coded source as three planes (the reference's coded_image layout)
             arr = np.roll(base["uyvy"][i % len(base["uyvy"])], 4 * (len(self.coded) + 1), axis=1)
             if planar:          # the same samples as three planes: UYVY = Cb Y0 Cr Y1
                 planes = [np.ascontiguousarray(arr[:, 1::2]), np.ascontiguousarray(arr[:, 0::4]), np.ascontiguousarray(arr[:, 2::4])]
-                pic = dev.DeviceCoded(planes, w, h, 2, dev._abi.CV_LAYOUT_PLANAR, dev.CV_MATRIX_709)
+                pic = dev.DeviceCoded(planes, w, h, 2, dev._abi.CV_LAYOUT_PLANAR, dev._abi.CV_MATRIX_709)
             else:
                 planes = [arr]
-                pic = dev.DeviceCoded(planes, w, h, 2, dev.CV_LAYOUT_UYVY, dev.CV_MATRIX_709)
+                pic = dev.DeviceCoded(planes, w, h, 2, dev._abi.CV_LAYOUT_UYVY, dev._abi.CV_MATRIX_709)
             self.coded.append(pic)
+            self.host_coded.append((arr, planar))
             for buffer, plane in zip(pic.buffers, planes):
-                pinned = PinnedArray(dev, plane.shape, np.uint8)
-                pinned.array[...] = plane
-                self.uploads.append((buffer.ptr, pinned))
+                mirror(buffer.ptr, plane, np.uint8)
 
         if name == "4k_8layer_composite":
             for i in range(8):
@@ -219,15 +278,16 @@ class InputSet:
             add_layer(1)
             self.out_u8 = dev.DeviceBuffer(w * h * 4)
             self.table = base["table"]
-            self.job = dev.make_job(a=self.layers[0], b=self.layers[1], mix_b=0.375, out_u8=self.out_u8,
+            self.job = dev.make_job(a=self.layers[0], b=self.layers[1], mix_b=self.mix_b, out_u8=self.out_u8,
                                     u8_table=self.table, full=full)
             self.d2h_bytes = w * h * 4
-        elif name == "4k_timeline":
+        elif name in ("4k_timeline", "4k_timeline_windows"):
             add_coded(0)
             add_coded(1)
+            windows = timeline_windows(w, h) if name.endswith("windows") else [None] * 3
             for i in range(3):
-                add_layer(i)
-            self.job = dev.make_job(out=self.out, a=self.coded[0], b=self.coded[1], mix_b=0.375, layers=self.layers)
+                add_layer(i, windows[i])
+            self.job = dev.make_job(out=self.out, a=self.coded[0], b=self.coded[1], mix_b=self.mix_b, layers=self.layers)
         elif name == "1080p_4layer_windows":
             for i, window in enumerate(WINDOWS_1080P):
                 add_layer(i, window)
@@ -236,7 +296,15 @@ class InputSet:
             raise SystemExit("unknown workload %r" % name)
 
         self.h2d_bytes = sum(p.nbytes for _, p in self.uploads)
-        self.result = PinnedArray(dev, (self.d2h_bytes,), np.uint8)
+        self.result = PinnedArray(dev, (self.d2h_bytes,), np.uint8) if pinned else None
+
+    def job_into(self, out):
+        """The same frame program writing into another output frame (so that every frame of a batch can be checked)."""
+        d = self.dev
+        if self.name == "1080p_cross_u8":
+            return d.make_job(a=self.layers[0], b=self.layers[1], mix_b=self.mix_b, out_u8=out, u8_table=self.table, full=self.full)
+        return d.make_job(out=out, a=self.coded[0] if self.coded else None, b=self.coded[1] if len(self.coded) > 1 else None,
+                          mix_b=self.mix_b if len(self.coded) > 1 else 0.0, layers=self.layers)
 
     def upload_inputs(self, stream):
         for dst, pinned in self.uploads:
@@ -246,16 +314,106 @@ class InputSet:
         src = self.out_u8.ptr if self.out_u8 is not None else self.out.c.data
         self.dev.check(self.dev.lib().cv_download(self.result.ptr, src, self.d2h_bytes, stream), "cv_download")
 
+    def output_array(self, out=None):
+        """The frame the last launch wrote: (h, w, 4) uint16 halves, or uint8 for the 8-bit workload."""
+        w, h = WORKLOADS[self.name][:2]
+        if self.out_u8 is not None:
+            return (out or self.out_u8).download(np.uint8, (h, w, 4))
+        return (out or self.out).download()
+
+    def free(self):
+        for _, p in self.uploads:
+            p.free()
+        if self.result is not None:
+            self.result.free()
+        for f in self.layers + [self.out]:
+            f.free()
+        for c in self.coded:
+            for b in c.buffers:
+                b.free()
+        if self.out_u8 is not None:
+            self.out_u8.free()
+        self.uploads, self.layers, self.coded = [], [], []
+
 
 def make_base(dev, name, seed):
     """A few distinct random source images; input sets use shifted copies (distinct memory, cheap to make)."""
-    w, h, _, _ = WORKLOADS[name]
+    w, h = WORKLOADS[name][:2]
     rng = np.random.default_rng(seed)
     base = {"layer": [synth_layer(rng, h, w) for _ in range(2)], "uyvy": [synth_uyvy(rng, h, w) for _ in range(2)]}
     if name == "1080p_cross_u8":
         base["table"] = dev.display_table(1.25)
     return base
 
+
+def count_sets(name):
+    return max(INPUT_SETS, int(np.ceil(RING_BYTES / workload_bytes(name))))
+
+
+# ----------------------------------------------------------------------------- the checker (oracle; never timed on our arm)
+
+def expected_output(inputs):
+    """What the oracle (oracle/liboracle.so, pinned bit for bit against the compiled reference) produces for the frame
+    program of `inputs`: (array, current_window tuple).  Test infrastructure: used after the timed region only."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oraclelib as O
+    orc = O.oracle()
+    name, full = inputs.name, inputs.full
+    w, h = WORKLOADS[name][:2]
+    out = O.HostFrame16(full)
+
+    def coded(arr, planar):
+        pic = O.CodedPicture(w, h, 2, O.LAYOUT_PLANAR if planar else O.LAYOUT_UYVY, O.MATRIX_709)
+        pic.set_samples(arr[:, 1::2], arr[:, 0::4], arr[:, 2::4])       # UYVY = Cb Y0 Cr Y1
+        return pic
+
+    layers = [O.HostFrame16(full, win, arr) for arr, win in inputs.host_layers]
+    pics = [coded(arr, planar) for arr, planar in inputs.host_coded]
+    arr = (O.Frame16 * max(1, len(layers)))(*[l.c for l in layers])
+
+    if name == "1080p_cross_u8":
+        orc.orc_cross_f16(C.byref(out.c), C.byref(layers[0].c), C.byref(layers[1].c), inputs.mix_b)
+        srgb, ramp = np.zeros(65536, np.uint16), np.zeros(65536, np.uint8)
+        orc.orc_build_lut(O.LUT_LINEAR_TO_SRGB, O.ptr(srgb))
+        orc.orc_build_intent_ramp(1.25, O.ptr(ramp))
+        u8 = np.zeros((h, w, 4), np.uint8)
+        orc.orc_encode_u8(C.byref(out.c), O.ptr(srgb), O.ptr(ramp), O.ptr(u8))
+        return u8, out.current.tuple()
+    if not pics:
+        orc.orc_composite_f16(C.byref(out.c), arr, len(layers))
+    elif not layers and len(pics) == 1:
+        orc.orc_reconstruct(C.byref(out.c), C.byref(pics[0].c))
+    else:
+        orc.orc_timeline_frame_f16(C.byref(out.c), C.byref(pics[0].c), C.byref(pics[1].c) if len(pics) > 1 else None,
+                                   inputs.mix_b if len(pics) > 1 else 0.0, arr, len(layers))
+    return out.array, out.current.tuple()
+
+
+def max_ulp(got, want):
+    """Largest distance between two arrays of raw half bits (or bytes), in units in the last place."""
+    if got.dtype == np.uint8:
+        return int(np.abs(got.astype(np.int32) - want.astype(np.int32)).max()) if got.size else 0
+    if np.array_equal(got, want):
+        return 0
+    def ordered(a):
+        a = a.astype(np.int32)
+        return np.where(a & 0x8000, -(a & 0x7FFF), a)
+    return int(np.abs(ordered(got) - ordered(want)).max())
+
+
+def check_sets(sets, which):
+    """Compares the outputs the last launches wrote for sets[i], i in `which`, with the oracle."""
+    worst, checked = 0, 0
+    for i in which:
+        want, window = expected_output(sets[i])
+        got = sets[i].output_array()
+        x0, y0, x1, y1 = window
+        worst = max(worst, max_ulp(got[y0:y1 + 1, x0:x1 + 1], want[y0:y1 + 1, x0:x1 + 1]))
+        checked += 1
+    return {"parity_checked": True, "max_ulp": worst, "frames_checked": checked}
+
+
+# ----------------------------------------------------------------------------- measurement
 
 def dist_setup(n_gpus):
     """torch.distributed for the barrier / max-over-ranks only (no data-path collective)."""
@@ -273,148 +431,193 @@ def dist_setup(n_gpus):
     return dist, rank, world
 
 
-def dist_max(dist, value):
+def dist_reduce(dist, value, op):
     if dist is None:
         return value
     import torch
     t = torch.tensor([value], dtype=torch.float64, device="cuda" if dist.get_backend() == "nccl" else "cpu")
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dist.all_reduce(t, op=getattr(dist.ReduceOp, op))
     return float(t.item())
 
 
-def dist_sum(dist, value):
-    if dist is None:
-        return value
-    import torch
-    t = torch.tensor([value], dtype=torch.float64, device="cuda" if dist.get_backend() == "nccl" else "cpu")
-    dist.all_reduce(t, op=dist.ReduceOp.SUM)
-    return float(t.item())
+class Bench:
+    """One device, one launching stream, the barrier of the job."""
+
+    def __init__(self, args):
+        from canvas_b200 import device as dev
+        self.dev, self.args = dev, args
+        self.dist, self.rank, self.world = dist_setup(args.gpus)
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        self.numa = pin_to_gpu_node(self.local) if not args.no_numa else None
+        dev.init(self.local)
+        self.lib = dev.lib()
+        self.stream = C.c_void_p()
+        dev.check(self.lib.cv_stream_create(C.byref(self.stream)), "cv_stream_create")
+        self.peak, self.peak_source = load_peaks()
+        self.traffic = load_traffic()
+
+    def barrier(self):
+        self.dev.check(self.lib.cv_device_sync(), "cv_device_sync")
+        if self.dist is not None:
+            self.dist.barrier()
+        self.dev.check(self.lib.cv_device_sync(), "cv_device_sync")
+
+    def build(self, name, pinned):
+        base = make_base(self.dev, name, 1234 + self.rank)
+        n_sets = count_sets(name)
+        return [InputSet(self.dev, name, base, pinned=pinned) for _ in range(n_sets)]
+
+    def measure(self, name, sets, steps, warmup, frames_per_step=None, sample_clocks=True):
+        """Device-resident throughput of `steps` steps; returns the pieces of a bench line."""
+        dev, lib = self.dev, self.lib
+        n_sets = len(sets)
+        per_step = frames_per_step or WORKLOADS[name][3]
+        per_step = max(n_sets, (per_step // n_sets) * n_sets)           # every step submits the same job array
+        jobs = (dev.FrameJob * per_step)(*[sets[f % n_sets].job for f in range(per_step)])
+
+        def step():
+            if self.args.no_batch:
+                for f in range(per_step):
+                    dev.check(lib.cv_render_frames(C.byref(jobs, f * C.sizeof(dev.FrameJob)), 1, self.stream), "cv_render_frames")
+            else:
+                dev.check(lib.cv_render_frames(jobs, per_step, self.stream), "cv_render_frames")
+
+        for _ in range(warmup):
+            step()
+        self.barrier()
+
+        sampler = ClockSampler(self.local) if sample_clocks else None
+        if sampler:
+            sampler.start()
+        launches_before = lib.cv_kernel_launches()
+        timer = dev.Timer(self.stream)
+        timer.begin()
+        for _ in range(steps):
+            step()
+        timer.end()
+        ms = timer.elapsed_ms()
+        self.barrier()
+        launches = lib.cv_kernel_launches() - launches_before
+        clocks = sampler.finish() if sampler else None
+
+        ms_max = dist_reduce(self.dist, ms, "MAX")
+        frames_rank = steps * per_step
+        frames_total = dist_reduce(self.dist, float(frames_rank), "SUM")
+        frame_bytes = workload_bytes(name)
+        kernel_ms = ms / max(1, launches)
+        frames_per_launch = frames_rank / max(1, launches)
+        achieved = frame_bytes * frames_per_launch / (kernel_ms * 1e-3) / 1e9
+        traffic = self.traffic.get(name)
+        return {
+            "value": frames_total / (ms_max * 1e-3), "ms_per_step": ms_max / steps, "frames_per_step": per_step,
+            "launches": int(launches), "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": self.peak, "unit": "GB/s", "frac": achieved / self.peak,
+                         "traffic": (traffic["dram_bytes_per_frame"] * frames_per_launch if traffic else None),
+                         "traffic_source": (traffic["source"] if traffic else None),
+                         "peak_source": self.peak_source, "algorithmic_bytes_per_frame": frame_bytes,
+                         "kernel_ms": kernel_ms, "frames_per_launch": frames_per_launch},
+        }
+
+    def e2e(self, sets, frames):
+        """Pinned host inputs -> HBM -> kernel -> pinned host result, every frame, several streams deep."""
+        dev, lib = self.dev, self.lib
+        n_sets = len(sets)
+        streams = []
+        for _ in range(min(n_sets, 4)):
+            s = C.c_void_p()
+            dev.check(lib.cv_stream_create(C.byref(s)), "cv_stream_create")
+            streams.append(s)
+
+        def run(count):
+            for f in range(count):
+                i = f % n_sets
+                st = streams[i % len(streams)]
+                sets[i].upload_inputs(st)
+                dev.render_frames([sets[i].job], st)
+                sets[i].download_result(st)
+            for s in streams:
+                dev.check(lib.cv_stream_sync(s), "cv_stream_sync")
+
+        run(n_sets)
+        self.barrier()
+        t0 = time.perf_counter()
+        run(frames)
+        seconds = time.perf_counter() - t0
+        self.barrier()
+        for s in streams:
+            lib.cv_stream_destroy(s)
+        seconds = dist_reduce(self.dist, seconds, "MAX")
+        return dist_reduce(self.dist, float(frames), "SUM") / seconds
 
 
 def run_ours(args):
-    from canvas_b200 import device as dev
-    for k in ("CV_LAYOUT_UYVY", "CV_MATRIX_709"):
-        setattr(dev, k, getattr(dev._abi, k))
+    B = Bench(args)
+    dev, name = B.dev, args.workload
+    w, h, _, _, description = WORKLOADS[name]
 
-    dist, rank, world = dist_setup(args.gpus)
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    dev.init(local)
-    lib = dev.lib()
+    sets = B.build(name, pinned=True)
+    m = B.measure(name, sets, args.steps, args.warmup)
+    # the outputs the timed launches wrote, against the oracle: the first and the last input set of the ring
+    parity = check_sets(sets, sorted({0, len(sets) - 1})) if not args.no_check else {"parity_checked": False}
 
-    name = args.workload
-    w, h, _, description = WORKLOADS[name]
-    frame_bytes = workload_bytes(name)
-    batch = not args.no_batch      # one cv_render_frames() call per step (the library launches one kernel per frame)
-    FRAMES_PER_STEP = frames_per_step(name)
-
-    base = make_base(dev, name, 1234 + rank)
-    n_sets = max(INPUT_SETS, int(np.ceil(RING_BYTES / frame_bytes)))
-    sets = [InputSet(dev, name, None, base) for _ in range(n_sets)]
-    stream = C.c_void_p()
-    dev.check(lib.cv_stream_create(C.byref(stream)), "cv_stream_create")
-
-    def step(first_frame):
-        if batch:
-            jobs = [sets[(first_frame + f) % n_sets].job for f in range(FRAMES_PER_STEP)]
-            dev.render_frames(jobs, stream)
-        else:
-            for f in range(FRAMES_PER_STEP):
-                dev.render_frames([sets[(first_frame + f) % n_sets].job], stream)
-
-    def barrier():
-        dev.check(lib.cv_device_sync(), "cv_device_sync")
-        if dist is not None:
-            dist.barrier()
-        dev.check(lib.cv_device_sync(), "cv_device_sync")
-
-    # ---- device-resident throughput ------------------------------------------------------------
-    frame = 0
-    for _ in range(args.warmup):
-        step(frame)
-        frame += FRAMES_PER_STEP
-    barrier()
-
-    sampler = ClockSampler(local)
-    sampler.start()
-    launches_before = lib.cv_kernel_launches()
-    timer = dev.Timer(stream)
-    timer.begin()
-    for _ in range(args.steps):
-        step(frame)
-        frame += FRAMES_PER_STEP
-    timer.end()
-    ms = timer.elapsed_ms()
-    barrier()
-    launches = lib.cv_kernel_launches() - launches_before
-    clocks = sampler.finish()
-
-    ms_max = dist_max(dist, ms)
-    frames_rank = args.steps * FRAMES_PER_STEP
-    frames_total = dist_sum(dist, float(frames_rank))
-    value = frames_total / (ms_max * 1e-3)
-
-    # ---- end to end: pinned host inputs -> HBM -> kernel -> pinned host result ------------------
-    streams = []
-    for _ in range(min(n_sets, 4)):
-        s = C.c_void_p()
-        dev.check(lib.cv_stream_create(C.byref(s)), "cv_stream_create")
-        streams.append(s)
-
-    def e2e_frames(count, first):
-        for f in range(count):
-            i = (first + f) % n_sets
-            st = streams[i % len(streams)]
-            sets[i].upload_inputs(st)
-            dev.render_frames([sets[i].job], st)
-            sets[i].download_result(st)
-
-    e2e_steps = max(1, min(args.steps, 4))
-    e2e_frames(n_sets, 0)
-    barrier()
-    t0 = time.perf_counter()
-    e2e_frames(e2e_steps * FRAMES_PER_STEP, 0)
-    for s in streams:
-        dev.check(lib.cv_stream_sync(s), "cv_stream_sync")
-    e2e_s = time.perf_counter() - t0
-    barrier()
-    e2e_s = dist_max(dist, e2e_s)
-    e2e_value = dist_sum(dist, float(e2e_steps * FRAMES_PER_STEP)) / e2e_s
-
-    peak, peak_source = load_peaks()
-    kernel_ms = ms / max(1, launches)
-    frames_per_launch = frames_rank / max(1, launches)
-    achieved = frame_bytes * frames_per_launch / (kernel_ms * 1e-3) / 1e9
+    e2e_frames = max(len(sets), min(args.steps * m["frames_per_step"], 96 if name.startswith("4k") else 960))
+    e2e_value = B.e2e(sets, e2e_frames)
+    h2d, d2h = sets[0].h2d_bytes, sets[0].d2h_bytes
 
     line = {
-        "metric": "f16 composite frames/sec (%s)" % name, "value": value, "unit": "frames/s",
-        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "metric": "f16 composite frames/sec (%s)" % name, "value": m["value"], "unit": "frames/s",
+        "n_gpus": B.world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": m["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f16 pixels, f32 arithmetic", "data": ("synthetic" if CONTENT == "noise" else "synthetic (%s-like coded sources)" % CONTENT) + (", planar 4:2:2" if PLANAR else ""),
         "config": {"workload": name, "description": description, "width": w, "height": h,
-                   "frames_per_step": FRAMES_PER_STEP, "input_sets": n_sets,
-                   "l2": "inputs larger than L2 (%.0f MB per frame, %d rotating sets)" % (frame_bytes / 1e6, n_sets),
-                   "sharding": "frames by index, one process per GPU, no collective"},
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": (NCU_TRAFFIC_PER_FRAME[name] * frames_per_launch if name in NCU_TRAFFIC_PER_FRAME else None),
-                     "traffic_source": "profiles/r1_final.md (ncu --set full, per frame x frames per launch)",
-                     "peak_source": peak_source, "algorithmic_bytes_per_frame": frame_bytes,
-                     "kernel_ms": kernel_ms},
-        "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": sets[0].h2d_bytes * FRAMES_PER_STEP,
-                "d2h_bytes_per_step": sets[0].d2h_bytes * FRAMES_PER_STEP, "steps": e2e_steps},
-        "gpu_launches": int(launches), "clocks": clocks,
+                   "frames_per_step": m["frames_per_step"], "input_sets": len(sets),
+                   "l2": "inputs larger than L2 (%.0f MB per frame, %d rotating sets)" % (workload_bytes(name) / 1e6, len(sets)),
+                   "sharding": "frames by index, one process per GPU, no collective", "numa": B.numa},
+        "roofline": m["roofline"],
+        "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d * m["frames_per_step"],
+                "d2h_bytes_per_step": d2h * m["frames_per_step"], "frames_timed": e2e_frames,
+                "h2d_bytes_per_frame": h2d, "d2h_bytes_per_frame": d2h},
+        "gpu_launches": m["launches"], "clocks": m["clocks"],
     }
+    line.update(parity)
+    for s in sets:
+        s.free()
+    sets = None
 
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    # ---- the other BASELINE.json configurations, about 0.3 s of device time each ------------------------------------
+    if not args.no_others:
+        others = []
+        for other in OTHER_WORKLOADS:
+            if other == name:
+                continue
+            osets = B.build(other, pinned=False)
+            om = B.measure(other, osets, steps=6, warmup=3, sample_clocks=False)
+            entry = {"workload": other, "value": om["value"], "unit": "frames/s", "ms_per_step": om["ms_per_step"],
+                     "frames_per_step": om["frames_per_step"], "steps": 6, "gpu_launches": om["launches"],
+                     "roofline_frac": om["roofline"]["frac"], "achieved_gbs": om["roofline"]["achieved"],
+                     "algorithmic_bytes_per_frame": om["roofline"]["algorithmic_bytes_per_frame"],
+                     "traffic": om["roofline"]["traffic"]}
+            if not args.no_check:
+                entry.update(check_sets(osets, [0]))
+            others.append(entry)
+            for s in osets:
+                s.free()
+        line["other_workloads"] = others
+
+    if B.rank == 0 and B.world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(name, seconds=20.0)
 
-    if rank == 0:
+    if B.rank == 0:
         print(json.dumps(line))
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+    if B.dist is not None:
+        B.dist.barrier()
+        B.dist.destroy_process_group()
 
 
 # ----------------------------------------------------------------------------- CPU baseline / reference arm
+
+REF_FAST_FLAGS = "-O3 -march=x86-64-v3 -mtune=generic -fno-math-errno -fno-signed-zeros (the reference's SConstruct:77,83 with x86-64-v3 for native, so that the build travels)"
+
 
 def host_cores():
     try:
@@ -425,7 +628,7 @@ def host_cores():
 
 def cpu_threads(name):
     """All usable host cores, bounded by memory (each in-flight 4K frame needs ~0.5 GB of f32 temporaries)."""
-    w, h, _, _ = WORKLOADS[name]
+    w, h = WORKLOADS[name][:2]
     per_thread = w * h * (8 + 16 + 16 + 8 + 8) * 1.2
     try:
         import psutil
@@ -443,7 +646,7 @@ def cpu_run(name, frames, threads):
     Returns (seconds, kind)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oraclelib as O
-    w, h, _, _ = WORKLOADS[name]
+    w, h = WORKLOADS[name][:2]
     full = (0, 0, w - 1, h - 1)
     rng = np.random.default_rng(99)
 
@@ -465,8 +668,10 @@ def cpu_run(name, frames, threads):
     # oracle port, frame-parallel through a thread pool (ctypes releases the GIL)
     from concurrent.futures import ThreadPoolExecutor
     orc = O.oracle()
-    layers = [O.HostFrame16(full, full, synth_layer(rng, h, w)) for _ in range(8 if "8layer" in name else (7 if "composite" in name else (4 if "4layer" in name else 3)))]
-    windowed = [O.HostFrame16(full, win, l.array) for l, win in zip(layers, WINDOWS_1080P)] if name == "1080p_4layer_windows" else []
+    n_layers = {"4k_8layer_composite": 8, "4k_composite_convert": 7, "1080p_4layer_windows": 4}.get(name, 3)
+    layers = [O.HostFrame16(full, full, synth_layer(rng, h, w)) for _ in range(n_layers)]
+    windows = WINDOWS_1080P if name == "1080p_4layer_windows" else ([full] + timeline_windows(w, h) if name == "4k_timeline_windows" else [])
+    windowed = [O.HostFrame16(full, win, l.array) for l, win in zip(layers, windows)]
     pics = [O.synth_coded(w, h, 5 + i, 2, O.LAYOUT_UYVY, O.MATRIX_709) for i in range(2)]
     srgb, ramp = np.zeros(65536, np.uint16), np.zeros(65536, np.uint8)
     orc.orc_build_lut(O.LUT_LINEAR_TO_SRGB, O.ptr(srgb))
@@ -490,6 +695,9 @@ def cpu_run(name, frames, threads):
         elif name == "4k_timeline":
             arr = (O.Frame16 * 3)(*[l.c for l in layers[:3]])
             orc.orc_timeline_frame_f16(C.byref(out.c), C.byref(pics[0].c), C.byref(pics[1].c), 0.375, arr, 3)
+        elif name == "4k_timeline_windows":
+            arr = (O.Frame16 * 3)(*[l.c for l in windowed[1:4]])
+            orc.orc_timeline_frame_f16(C.byref(out.c), C.byref(pics[0].c), C.byref(pics[1].c), 0.375, arr, 3)
         elif name == "1080p_4layer_windows":
             arr = (O.Frame16 * 4)(*[l.c for l in windowed])
             orc.orc_composite_f16(C.byref(out.c), arr, 4)
@@ -508,13 +716,19 @@ def cpu_run(name, frames, threads):
 
 
 def cpu_baseline(name, seconds=20.0):
-    """Bounded sample of the same workload on the host cores (about `seconds` of CPU work)."""
+    """Bounded sample of the same workload on the host cores (about `seconds` of CPU work), all cores and -- what the
+    reference itself does: one frame on one thread (src/process/VideoPullQueue.c:110, main.c:120-167) -- one thread."""
     threads = cpu_threads(name)
-    t, kind = cpu_run(name, threads, threads)                   # calibration: one frame per thread
-    frames = int(max(threads, min(64 * threads, threads * round(seconds / max(t, 1e-3)))))
+    t0, kind = cpu_run(name, threads, threads)                  # calibration: one frame per thread
+    frames = int(max(threads, min(64 * threads, threads * round(seconds * 0.75 / max(t0, 1e-3)))))
     t, kind = cpu_run(name, frames, threads)
+    single = int(max(2, min(64, round(seconds * 0.25 / max(t0, 1e-3)))))       # a frame alone takes at most t0
+    t1, _ = cpu_run(name, single, 1)
     return {"value": frames / t, "unit": "frames/s", "cores": threads, "kind": kind,
-            "sample": "%d frames of %s, %d frames in flight (one per thread), %.1f s" % (frames, name, threads, t)}
+            "sample": "%d frames of %s, %d frames in flight (one per thread), %.1f s" % (frames, name, threads, t),
+            "one_thread": {"value": single / t1, "unit": "frames/s", "cores": 1,
+                           "sample": "%d frames on one thread, %.1f s" % (single, t1)},
+            "flags": REF_FAST_FLAGS if kind == "reference" else "oracle/Makefile: -O2 -ffp-contract=off"}
 
 
 def run_reference(args):
@@ -523,7 +737,7 @@ def run_reference(args):
     if rank != 0:
         return
     name = args.workload
-    w, h, _, description = WORKLOADS[name]
+    w, h, _, _, description = WORKLOADS[name]
     threads = cpu_threads(name)
     t1, kind = cpu_run(name, threads, threads)
     per_step = int(max(threads, min(16 * threads, threads * round(8.0 / max(t1, 1e-3)))))   # ~8 s per step
@@ -543,7 +757,8 @@ def run_reference(args):
         "config": {"workload": name, "description": description, "width": w, "height": h,
                    "frames_per_step": per_step, "note": "CPU reference arm: steps bounded to %d x %d frames" % (steps, per_step)},
         "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": kind,
-                         "sample": "%d steps x %d frames of %s, %d frames in flight" % (steps, per_step, name, threads)},
+                         "sample": "%d steps x %d frames of %s, %d frames in flight" % (steps, per_step, name, threads),
+                         "flags": REF_FAST_FLAGS if kind == "reference" else "oracle/Makefile: -O2 -ffp-contract=off"},
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -553,15 +768,18 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="4k_8layer_composite", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-others", action="store_true", help="skip the other_workloads array")
+    ap.add_argument("--no-check", action="store_true", help="skip the oracle comparison after the timed region")
+    ap.add_argument("--no-numa", action="store_true", help="do not pin the process to the GPU's NUMA node")
     ap.add_argument("--planar", action="store_true", help="4:2:2 sources as three planes instead of packed UYVY")
     ap.add_argument("--content", default="noise", choices=["noise", "video"],
                     help="coded sources: independent random bytes (default) or smooth picture-like content")
-    ap.add_argument("--no-batch", action="store_true", help="one launch per frame even for microsecond kernels")
+    ap.add_argument("--no-batch", action="store_true", help="one cv_render_frames() call per frame")
     args = ap.parse_args()
     global CONTENT, PLANAR
     CONTENT, PLANAR = args.content, args.planar

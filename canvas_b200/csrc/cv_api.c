@@ -274,6 +274,22 @@ static int build_job( cv_frame_job *job, const BuildOptions *opt, DevJob *dj, in
             (dj->bottom_mode == DEV_BOTTOM_CROSS && dj->b.kind == CV_SRC_F32))) )
         dj->flags |= JOB_FLAG_EXACT;
 
+    /* The shared-reciprocal division of the fast path assumes that a non-zero alpha is >= 2^-48 (a half's smallest
+     * alpha 2^-24 squared).  A positive mix below 2^-24 breaks that bound (alpha = a * mix may fall under the
+     * reciprocal's floor): such jobs keep the IEEE-division path. */
+    {
+        const float floor_mix = 5.9604645e-8f;      /* 2^-24 */
+        int tiny = 0;
+        if( dj->bottom_mode == DEV_BOTTOM_CROSS )
+            tiny = (dj->mix_a > 0.0f && dj->mix_a < floor_mix) || (dj->mix_b > 0.0f && dj->mix_b < floor_mix);
+        else if( dj->bottom_mode == DEV_BOTTOM_SINGLE )
+            tiny = dj->single_alpha > 0.0f && dj->single_alpha < floor_mix;
+        for( int i = 0; i < n; i++ )
+            tiny = tiny || dj->layer[i].mix < floor_mix;         /* layers with mix 0 were dropped above */
+        if( tiny )
+            dj->flags |= JOB_FLAG_EXACT;
+    }
+
     /* the common workspace case: full-coverage layers, no window tests needed in the kernel */
     if( *shape == KB_LAYERS && *px == 2 && ((under.x0 - dj->full_x) & 1) == 0 && ((under.x1 - under.x0 + 1) & 1) == 0 ) {
         int simple = 1;

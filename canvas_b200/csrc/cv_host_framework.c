@@ -79,7 +79,7 @@ static size_t window_pixels( const box2i *w ) {
 
 static void gpu_half_from_float( half *out, const float *in, int count ) {
     if( count <= 0 || !host_ready() ) return;
-    Scratch src, dst;
+    Scratch src = { 0 }, dst = { 0 };
     if( !scratch_up( &src, in, sizeof(float) * (size_t) count ) && !scratch_up( &dst, NULL, sizeof(half) * (size_t) count ) &&
             !cv_half_from_float( (half *) dst.dev, (const float *) src.dev, (size_t) count, NULL ) )
         scratch_down( &dst, out );
@@ -89,7 +89,7 @@ static void gpu_half_from_float( half *out, const float *in, int count ) {
 
 static void gpu_half_to_float( float *out, const half *in, int count ) {
     if( count <= 0 || !host_ready() ) return;
-    Scratch src, dst;
+    Scratch src = { 0 }, dst = { 0 };
     if( !scratch_up( &src, in, sizeof(half) * (size_t) count ) && !scratch_up( &dst, NULL, sizeof(float) * (size_t) count ) &&
             !cv_half_to_float( (float *) dst.dev, (const half *) src.dev, (size_t) count, NULL ) )
         scratch_down( &dst, out );
@@ -99,7 +99,7 @@ static void gpu_half_to_float( float *out, const half *in, int count ) {
 
 static void gpu_half_lookup( const half *table, half *out, const half *in, int count ) {
     if( count <= 0 || !host_ready() ) return;
-    Scratch tab, buf;
+    Scratch tab = { 0 }, buf = { 0 };
     if( !scratch_up( &tab, table, sizeof(half) * HALF_COUNT ) && !scratch_up( &buf, in, sizeof(half) * (size_t) count ) &&
             !cv_half_lookup( (const half *) tab.dev, (half *) buf.dev, (const half *) buf.dev, (size_t) count, NULL ) )
         scratch_down( &buf, out );
@@ -127,7 +127,7 @@ void init_half( void ) {
 
 static void transfer( int which, half *out, const half *in, size_t count ) {
     if( !count || !host_ready() ) return;
-    Scratch buf;
+    Scratch buf = { 0 };
     if( !scratch_up( &buf, in, sizeof(half) * count ) && !cv_transfer( which, (half *) buf.dev, (const half *) buf.dev, count, NULL ) )
         scratch_down( &buf, out );
     scratch_free( &buf );

@@ -40,13 +40,14 @@ int64_t cv_timeline_frames_of( int slot, int64_t first, int64_t last, int chunk,
     return mine;
 }
 
-/* AnimationFunc.c:439-446 for a two-point linear segment: lerp in double, then (float) */
+/* AnimationFunc.c:439-446 for a two-point linear segment: (right * (f - left_frame) + left * (right_frame - f)) / distance
+ * in double -- the reference's own expression, so that the (float) below rounds the same double -- then (float) */
 static float ramp_value( const cv_timeline_item *it, int64_t source_frame ) {
     if( it->ramp_length <= 0 ) return it->mix_first;
-    const double t = (double)( source_frame - it->ramp_start ) / (double) it->ramp_length;
-    if( t <= 0.0 ) return it->mix_first;
-    if( t >= 1.0 ) return it->mix_last;
-    return (float)( (double) it->mix_first * (1.0 - t) + (double) it->mix_last * t );
+    if( source_frame <= it->ramp_start ) return it->mix_first;
+    if( source_frame >= it->ramp_start + it->ramp_length ) return it->mix_last;
+    const double f = (double) source_frame, left = (double) it->ramp_start, right = (double)( it->ramp_start + it->ramp_length );
+    return (float)( ((double) it->mix_last * (f - left) + (double) it->mix_first * (right - f)) / (right - left) );
 }
 
 static const cv_source *clip_frame( const cv_clip *clip, int64_t source_frame ) {

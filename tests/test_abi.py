@@ -85,3 +85,18 @@ def test_host_tables_match_oracle(lib):
     want = np.zeros(65536, np.uint8)
     O.oracle().orc_build_gamma45(O.ptr(want))
     assert np.array_equal(np.ctypeslib.as_array(lib.cv_host_gamma45_ramp(), shape=(65536,)), want)
+
+
+def test_nothing_but_the_headers_is_exported(lib):
+    """The drop-in exports include/*.h and nothing else: no kernel stubs, no cvi_* internals, no CUDA runtime
+    (canvas_b200/csrc/exports.map)."""
+    out = subprocess.run(["nm", "-D", "--defined-only", os.path.join(ROOT, "canvas_b200", "libcanvas_b200.so")],
+                         capture_output=True, text=True, check=True).stdout
+    exported = {line.split()[-1] for line in out.splitlines() if line.strip()}
+    declared = declared_functions("canvas_b200.h") | declared_functions("framework.h") | {
+        "init_half", "half_convert_from_float", "half_convert_to_float", "half_convert_from_float_fast",
+        "half_convert_to_float_fast", "half_lookup"}
+    extra = sorted(exported - declared)
+    assert not extra, "exported but not declared in include/*.h: %s" % extra
+    missing = sorted(declared - exported)
+    assert not missing, "declared in include/*.h but not exported: %s" % missing
