@@ -440,6 +440,14 @@ def dist_reduce(dist, value, op):
     return float(t.item())
 
 
+def dist_max(dist, value):
+    return dist_reduce(dist, value, "MAX")
+
+
+def dist_sum(dist, value):
+    return dist_reduce(dist, value, "SUM")
+
+
 class Bench:
     """One device, one launching stream, the barrier of the job."""
 
@@ -500,9 +508,9 @@ class Bench:
         launches = lib.cv_kernel_launches() - launches_before
         clocks = sampler.finish() if sampler else None
 
-        ms_max = dist_reduce(self.dist, ms, "MAX")
+        ms_max = dist_max(self.dist, ms)
         frames_rank = steps * per_step
-        frames_total = dist_reduce(self.dist, float(frames_rank), "SUM")
+        frames_total = dist_sum(self.dist, float(frames_rank))
         frame_bytes = workload_bytes(name)
         kernel_ms = ms / max(1, launches)
         frames_per_launch = frames_rank / max(1, launches)
@@ -546,8 +554,8 @@ class Bench:
         self.barrier()
         for s in streams:
             lib.cv_stream_destroy(s)
-        seconds = dist_reduce(self.dist, seconds, "MAX")
-        return dist_reduce(self.dist, float(frames), "SUM") / seconds
+        seconds = dist_max(self.dist, seconds)
+        return dist_sum(self.dist, float(frames)) / seconds
 
 
 def run_ours(args):
