@@ -131,6 +131,34 @@ enum { KB_LAYERS = 0,           /* no bottom sources: layer[0] is fetched, the r
        KB_CODED = 2,            /* bottom from a/b with at least one coded source: 128 KiB table in SMEM */
        KB_COUNT = 3 };
 
+/* ---- windowed jobs as rectangles of constant coverage (cv_rects.c -> k_rect) ---- */
+
+enum { CV_RECT_MAX_BANDS = 40, CV_RECT_MAX_PIECES = 2048 };
+enum { RECT_FIRST_COPY = 1,     /* nothing lies below the first covering layer: it is fetched as it is */
+       RECT_RAGGED = 2 };       /* a one-pair column split by a window edge: per-item code */
+
+/* what one warp renders at a time: `pairs` pixel pairs of one row starting at pair column pair0 (relative to item_x0) */
+typedef struct RectPiece {
+    uint32_t pair0;
+    uint16_t pairs;
+    uint8_t bottom;             /* bit 0: source a covers it, bit 1: source b */
+    uint8_t flags;              /* RECT_* */
+    uint32_t mask;              /* bit k: layer k covers it */
+    uint32_t reserved;
+} RectPiece;
+
+/* rows y0 .. y0 + rows - 1 share one list of `ppr` pieces per row (entries first_entry ..).  The kernel's unit of work
+ * is a piece over a GROUP of up to rows_per_unit consecutive rows of its band (decoded once, then walked row by row);
+ * units of a band are numbered group-major, `ustart` = units of the bands above in one frame. */
+typedef struct RectBand { int32_t y0; uint32_t rows, ppr, magic, first_entry, ustart; } RectBand;
+
+typedef struct RectPlan {
+    int32_t n_bands;
+    uint32_t n_entries, rows_per_unit, units_per_frame, frame_magic;
+    uint64_t row_pieces_per_frame;          /* sum over bands of rows x ppr (statistics, load balance) */
+    RectBand band[CV_RECT_MAX_BANDS];
+} RectPlan;
+
 /* ---- per-device state -------------------------------------------------------------- */
 
 typedef struct CvDevice {
@@ -148,6 +176,7 @@ typedef struct CvDevice {
     DevJob *job_ring_host;              /* pinned mirror */
     uint32_t job_ring_size, job_ring_pos;
     cudaEvent_t *job_ring_events;       /* one per ring segment */
+    RectPiece *piece_ring_dev, *piece_ring_host;    /* CV_RECT_MAX_PIECES entries per job-ring segment (k_rect's piece lists) */
     pthread_mutex_t lock;               /* guards the job ring and the pool */
 } CvDevice;
 
@@ -183,6 +212,17 @@ int cvi_launch_gain_offset( const FillArgs *args, cudaStream_t stream );
 int cvi_launch_color( const ColorArgs *args, cudaStream_t stream );
 int cvi_launch_subsample_mpeg2( const Mpeg2Args *args, cudaStream_t stream );
 int cvi_kernels_init( void );                       /* per-device function attributes */
+
+/* rectangles of constant coverage (cv_rects.c): 0 and a filled plan, or -1 when the job is not one the rectangle
+ * kernel takes (f32 frames, layer mixes other than 1, 4:1:1 sources, too many pieces) */
+int cvi_rect_applies( const DevJob *job );
+int cvi_rect_plan( const DevJob *job, int ppl, int rows_per_unit, RectPlan *plan, RectPiece *pieces, int capacity );
+/* cv_rect.cu: the rectangle-walking kernel (CV_NO_RECT=1 disables it: windowed jobs then use k_seg's classifying mode) */
+int cvi_rect_enabled( void );
+int cvi_rect_ppl( const DevJob *job );          /* pixel pairs per lane and piece the kernel will be launched with */
+int cvi_rect_rows( const DevJob *job, int ppl, int count );     /* rows per unit of work for a launch over `count` frames */
+int cvi_launch_rect( int shape, int ppl, const DevJob *job, const DevJob *dev_jobs, int count, const RectPlan *plan,
+                     const RectPiece *dev_pieces, cudaStream_t stream );
 uint32_t cvi_div_magic( uint32_t d );
 
 #ifdef __cplusplus

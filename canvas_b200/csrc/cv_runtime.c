@@ -254,6 +254,8 @@ void cv_shutdown( void ) {
         cudaFree( dev->flush_buf );
         cudaFree( dev->job_ring_dev );
         cudaFreeHost( dev->job_ring_host );
+        cudaFree( dev->piece_ring_dev );
+        cudaFreeHost( dev->piece_ring_host );
         if( dev->job_ring_events ) {
             for( int i = 0; i < 8; i++ ) cudaEventDestroy( dev->job_ring_events[i] );
             free( dev->job_ring_events );
