@@ -28,6 +28,8 @@ struct RectArgs {
     uint32_t all_units;                     /* frames x plan.units_per_frame */
 };
 
+#define CV_RECT_PARK_BYTES 576u          /* per warp: 64 bytes lane-uniform + 32 x 16 bytes per lane (the unit waiting to be rendered) */
+
 #ifndef CV_RECT_MAX_THREADS
 #define CV_RECT_MAX_THREADS 384       /* 168 registers: two units and the 4:2:2 groups of two rows stay in registers (512 threads spilled them) */
 #endif
@@ -81,16 +83,43 @@ k_rect( const __grid_constant__ DevJob J0, const DevJob *__restrict__ jobs, cons
     const uint32_t first = blockIdx.x * warps + warp, stride = gridDim.x * warps;
     const uint32_t mine = first < A.all_units ? (A.all_units - first - 1) / stride + 1 : 0;
 
-    /* a unit: one piece over up to plan.rows_per_unit rows; `src` / `dst16` are this LANE's addresses */
+    /* a unit: one piece over up to plan.rows_per_unit rows; `src` / `dst16` are this LANE's addresses.  The unit being
+     * rendered lives in registers; the NEXT one is decoded a whole unit ahead and waits in shared memory (one record per
+     * warp: the lane-uniform part once, the lanes' source addresses next to it), so that looking ahead costs no registers
+     * in the row loop. */
     struct Unit {
         const DevJob *job;
+        char *dst16;                    /* this lane's first output pair */
         int y, x0;
         uint32_t rows, pairs, mask, bottom, flags;
         uint32_t row_bytes;             /* what one row's copies bring into the ring (the mbarrier's transaction count) */
-        uint32_t src_pitch;
-        const char *src;                /* this lane's ring slot: where its next row comes from (NULL: not covered) */
-        char *dst16;                    /* this lane's first output pair */
         float mix_a, mix_b;
+        const char *src;                /* this lane's ring slot: where its next row comes from (NULL: not covered) */
+        uint32_t src_pitch;
+    };
+    struct ParkedCommon { const DevJob *job; char *dst16; int y, x0; uint32_t rows, pairs, mask, bottom, flags, row_bytes; float mix_a, mix_b; };
+    struct ParkedLane { const char *src; uint32_t src_pitch, pad; };
+    static_assert( sizeof(ParkedCommon) == 56 && sizeof(ParkedLane) == 16, "parked unit layout" );
+    unsigned char *const park_base = smem + table_bytes + (((size_t)( warps + 1 ) * 16 + 127) & ~(size_t) 127) + (size_t) warps * 2 * A.stage_bytes
+                                   + (size_t) warp * CV_RECT_PARK_BYTES;
+    ParkedCommon *const park_common = reinterpret_cast<ParkedCommon *>( park_base );
+    ParkedLane *const park_lane = reinterpret_cast<ParkedLane *>( park_base + 64 ) + lane;
+
+    auto park = [&]( const Unit &U ) {
+        if( lane == 0 ) {
+            ParkedCommon c;
+            c.job = U.job; c.dst16 = U.dst16; c.y = U.y; c.x0 = U.x0; c.rows = U.rows; c.pairs = U.pairs; c.mask = U.mask;
+            c.bottom = U.bottom; c.flags = U.flags; c.row_bytes = U.row_bytes; c.mix_a = U.mix_a; c.mix_b = U.mix_b;
+            *park_common = c;
+        }
+        park_lane->src = U.src; park_lane->src_pitch = U.src_pitch;
+        __syncwarp();
+    };
+    auto unpark = [&]( Unit &U ) {
+        const ParkedCommon c = *park_common;
+        U.job = c.job; U.dst16 = c.dst16 + lane * 16; U.y = c.y; U.x0 = c.x0; U.rows = c.rows; U.pairs = c.pairs; U.mask = c.mask;
+        U.bottom = c.bottom; U.flags = c.flags; U.row_bytes = c.row_bytes; U.mix_a = c.mix_a; U.mix_b = c.mix_b;
+        U.src = park_lane->src; U.src_pitch = park_lane->src_pitch;
     };
 
     auto decode = [&]( uint32_t index, Unit &U ) {
@@ -111,7 +140,7 @@ k_rect( const __grid_constant__ DevJob J0, const DevJob *__restrict__ jobs, cons
         U.x0 = J0.item_x0 + 2 * (int) e.pair0;
         U.pairs = e.pairs; U.mask = e.mask; U.bottom = e.bottom; U.flags = e.flags;
         U.mix_a = J.mix_a; U.mix_b = J.mix_b;
-        U.dst16 = static_cast<char *>( J.out16 ) + ((int64_t)( U.y - J0.full_y ) * J0.out_pitch + ( U.x0 - J0.full_x )) * 8 + lane * 16;
+        U.dst16 = static_cast<char *>( J.out16 ) + ((int64_t)( U.y - J0.full_y ) * J0.out_pitch + ( U.x0 - J0.full_x )) * 8;   /* + lane * 16 when unparked */
 
         const bool ragged = (e.flags & RECT_RAGGED) != 0;
         U.src = NULL; U.src_pitch = 0;
@@ -156,15 +185,17 @@ k_rect( const __grid_constant__ DevJob J0, const DevJob *__restrict__ jobs, cons
         }
     };
 
-    Unit cur, nxt;
+    Unit cur;
     CodedRegs<PPL> ca, cb, na, nbg;
     #pragma unroll
     for( int q = 0; q < PPL; q++ ) ca.w[q] = cb.w[q] = na.w[q] = nbg.w[q] = 0x80808080u;
     ca.extra = cb.extra = na.extra = nbg.extra = 0x80808080u;
 
     if( mine ) {
-        decode( first, nxt );
-        issue_row( nxt, nxt.y, 0, na, nbg );
+        Unit head;
+        decode( first, head );
+        issue_row( head, head.y, 0, na, nbg );
+        park( head );
     }
 
     if( table_bytes ) {
@@ -180,10 +211,14 @@ k_rect( const __grid_constant__ DevJob J0, const DevJob *__restrict__ jobs, cons
 
     uint32_t it = 0;                /* rows rendered so far: ring stage and barrier phase */
     for( uint32_t u = 0; u < mine; u++ ) {
-        cur = nxt;
+        unpark( cur );
+        __syncwarp();                   /* everyone has taken the parked unit before the next one is written over it */
         const bool more = u + 1 < mine;
-        if( more )
-            decode( first + (u + 1) * stride, nxt );
+        if( more ) {
+            Unit ahead;
+            decode( first + (u + 1) * stride, ahead );
+            park( ahead );
+        }
 
         const DevJob &J = *cur.job;
         char *dst16 = cur.dst16;
@@ -194,7 +229,12 @@ k_rect( const __grid_constant__ DevJob J0, const DevJob *__restrict__ jobs, cons
             const int y = cur.y + (int) r;
             ca = na; cb = nbg;
             if( r + 1 < cur.rows ) issue_row( cur, y + 1, s ^ 1, na, nbg );
-            else if( more ) issue_row( nxt, nxt.y, s ^ 1, na, nbg );
+            else if( more ) {           /* the first row of the next unit: its record, with the advanced source address written back */
+                Unit ahead;
+                unpark( ahead );
+                issue_row( ahead, ahead.y, s ^ 1, na, nbg );
+                park_lane->src = ahead.src;
+            }
 
             if( A.slots )
                 mbar_wait( bars + s, (it >> 1) & 1u );
@@ -389,7 +429,7 @@ static int launch_rect_ppl( CvDevice *dev, const DevJob *job, const DevJob *dev_
     int warps = tables ? max_warps : small_warps;
     size_t smem;
     for( ;; ) {
-        smem = tables + (((size_t)( warps + 1 ) * 16 + 127) & ~(size_t) 127) + (size_t) warps * 2 * A.stage_bytes;
+        smem = tables + (((size_t)( warps + 1 ) * 16 + 127) & ~(size_t) 127) + (size_t) warps * 2 * A.stage_bytes + (size_t) warps * CV_RECT_PARK_BYTES;
         if( smem <= limit || warps == 1 ) break;
         warps--;
     }
