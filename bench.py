@@ -558,6 +558,198 @@ class Bench:
         return dist_sum(self.dist, float(frames)) / seconds
 
 
+def plugin_e2e(B, name, sets, check=True):
+    """The same workload through the REFERENCE's interface with host buffers (include/framework.h): the layers of each
+    input set are host f16 frames wrapped as video sources, placed on a workspace with workspace_add_item, and the
+    composite is pulled with video_get_frame_f16(&workspace_source, frame, &host_frame) from several threads -- the
+    calls canvas_b200/csrc/client/host_client.c makes, and the calls the reference arm makes against the reference's own C
+    (oracle/ref_harness.c).  Frames live in ordinary (pageable) host memory, as the reference's PyMem_Malloc frames do."""
+    from canvas_b200 import _abi as A
+    w, h = WORKLOADS[name][:2]
+    full = A.Box2i(0, 0, w - 1, h - 1)
+    client = C.CDLL(os.path.join(ROOT, "canvas_b200", "libcanvas_client.so"))
+    client.client_timeline_create.restype = C.c_void_p
+    client.client_timeline_create.argtypes = [C.POINTER(A.FrameF16), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int64),
+                                              C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.c_int]
+    client.client_time_timeline.restype = C.c_int64
+    client.client_time_timeline.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(A.FrameF16)]
+    client.client_timeline_get_frame_f16.argtypes = [C.c_void_p, C.c_int, C.POINTER(A.FrameF16)]
+    client.client_timeline_free.argtypes = [C.c_void_p]
+
+    n_layers, n_sets = len(sets[0].host_layers), len(sets)
+    keep, frames = [], (A.FrameF16 * (n_layers * n_sets))()
+    for k in range(n_layers):               # clip k = layer k of every input set: timeline frame f shows set f mod n_sets
+        for i, inputs in enumerate(sets):
+            arr, window = inputs.host_layers[k]
+            arr = np.ascontiguousarray(arr)
+            keep.append(arr)
+            f = frames[k * n_sets + i]
+            f.data, f.full_window, f.current_window = arr.ctypes.data, full, A.Box2i(*window)
+    ints, longs = C.c_int * n_layers, C.c_int64 * n_layers
+    tl = client.client_timeline_create(frames, ints(*[k * n_sets for k in range(n_layers)]), ints(*([n_sets] * n_layers)),
+                                       longs(*([0] * n_layers)), longs(*([1 << 30] * n_layers)), longs(*([0] * n_layers)),
+                                       longs(*range(n_layers)), n_layers)
+
+    threads = max(1, min(16, host_cores()))
+    outs_np = [np.zeros((h, w, 4), np.uint16) for _ in range(threads)]
+    outs = (A.FrameF16 * threads)()
+    for t in range(threads):
+        outs[t].data, outs[t].full_window = outs_np[t].ctypes.data, full
+
+    client.client_time_timeline(tl, 0, threads, threads, outs)            # warm-up: contexts, slabs, pool
+    B.barrier()
+    count = 8 * threads if name.startswith("4k") else 64 * threads
+    ns = client.client_time_timeline(tl, 0, count, threads, outs)
+    B.barrier()
+    seconds = dist_max(B.dist, ns * 1e-9)
+    result = {"value": dist_sum(B.dist, float(count)) / seconds, "unit": "frames/s", "threads": threads, "frames_timed": count,
+              "call": "video_get_frame_f16(workspace_as_video_source(...), frame, &host_frame) over %d host-frame sources per frame "
+                      "(include/framework.h; pageable host memory in and out)" % n_layers}
+    if check:
+        one = A.FrameF16()
+        got = np.zeros((h, w, 4), np.uint16)
+        one.data, one.full_window = got.ctypes.data, full
+        client.client_timeline_get_frame_f16(tl, 0, C.byref(one))
+        want, window = expected_output(sets[0])
+        x0, y0, x1, y1 = window
+        result["parity_checked"] = True
+        result["max_ulp"] = max_ulp(got[y0:y1 + 1, x0:x1 + 1], want[y0:y1 + 1, x0:x1 + 1]) if one.current_window.tuple() == window else -1
+    client.client_timeline_free(tl)
+    return result
+
+
+def scheduler_bench(B, n_gpus, frames=1000, chunk=16, ring=32, clip=4):
+    """BASELINE.json configs[4] through the C scheduler: a 3840x2160, `frames`-frame timeline -- two 4:2:2 clips crossfading
+    under a linear ramp + three f16 overlay clips with PARTIAL windows -- rendered by ONE cv_timeline_render() call that
+    hands chunks of frames to the GPUs of this box (one worker thread, a compute and a copy stream per GPU, no collective).
+      resident   every clip resident on every GPU, f16 output left in HBM (the device-side capability of the scheduler);
+      pulled_u8  end to end: the 4:2:2 pictures are PULLED from pinned host memory through coded_image_source.getFrame
+                 (4 B/px host->device per frame), overlays resident (static graphics), the 8-bit display encode of every
+                 frame copied to pinned host memory from the sink (4 B/px device->host)."""
+    from canvas_b200 import _abi as A
+    dev, lib = B.dev, B.lib
+    w, h = 3840, 2160
+    full = (0, 0, w - 1, h - 1)
+    windows = timeline_windows(w, h)
+    rng = np.random.default_rng(7)
+    base_uyvy = rng.integers(16, 236, size=(h, w * 2), dtype=np.uint8)
+    base_layer = synth_layer(rng, h, w)
+
+    client = C.CDLL(os.path.join(ROOT, "canvas_b200", "libcanvas_client.so"))
+    client.client_coded_clip_create.restype = C.c_void_p
+    client.client_coded_clip_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    client.client_coded_clip_source.restype = C.POINTER(A.CodedImageSource)
+    client.client_coded_clip_source.argtypes = [C.c_void_p]
+
+    keep, clips, pulls = [], {}, {}
+    for name in ("a", "b", "o0", "o1", "o2"):
+        arr = (A.Clip * n_gpus)()
+        for g in range(n_gpus):
+            dev.init(g)
+            srcs = (A.Source * clip)()
+            for k in range(clip):
+                if name in ("a", "b"):
+                    d = dev.DeviceCoded([np.roll(base_uyvy, 4 * (k + 1) + (64 if name == "b" else 0), axis=1)], w, h, 2,
+                                        A.CV_LAYOUT_UYVY, A.CV_MATRIX_709)
+                    srcs[k].kind, srcs[k].coded = A.CV_SRC_CODED, d.c
+                else:
+                    d = dev.DeviceFrame16.from_numpy(np.roll(base_layer, 17 * k + 1, axis=1), full, windows[int(name[1])])
+                    srcs[k].kind, srcs[k].f16 = A.CV_SRC_F16, d.c
+                keep.append(d)
+            arr[g].frames, arr[g].count = srcs, clip
+            keep.append(srcs)
+        clips[name] = arr
+    dev.init(B.local)
+    for name in ("a", "b"):                 # the same pictures in pinned host memory, behind coded_image_source.getFrame
+        planes = (C.c_void_p * clip)()
+        for k in range(clip):
+            pic = np.roll(base_uyvy, 4 * (k + 1) + (64 if name == "b" else 0), axis=1)
+            pinned = PinnedArray(dev, pic.shape, np.uint8)
+            pinned.array[...] = pic
+            planes[k] = pinned.ptr.value
+            keep.append(pinned)
+        stride, lines = (C.c_int * 1)(2 * w), (C.c_int * 1)(h)
+        p = A.Pull()
+        p.coded = client.client_coded_clip_source(client.client_coded_clip_create(planes, clip, 1, stride, lines))
+        p.format.layout, p.format.width, p.format.height, p.format.sub_x, p.format.matrix = A.CV_LAYOUT_UYVY, w, h, 2, A.CV_MATRIX_709
+        pulls[name] = p
+        keep += [planes, stride, lines]
+
+    def make_items(pulled):
+        items = (A.TimelineItem * 4)()
+        items[0].x, items[0].length, items[0].z, items[0].offset = 0, frames, 0, 0
+        if pulled:
+            items[0].pull, items[0].pull_b = C.pointer(pulls["a"]), C.pointer(pulls["b"])
+        else:
+            items[0].clips, items[0].clips_b = clips["a"], clips["b"]
+        items[0].mix_first, items[0].mix_last, items[0].ramp_start, items[0].ramp_length = 0.0, 1.0, -1, frames + 1
+        for i in range(3):
+            it = items[1 + i]
+            it.x, it.length, it.z, it.offset, it.clips = 0, frames, 1 + i, i, clips["o%d" % i]
+        return items
+
+    targets, pinned_out, u8_rings = (A.TimelineTarget * n_gpus)(), [], []
+    for g in range(n_gpus):
+        dev.init(g)
+        outs = (A.FrameF16 * ring)()
+        bufs = (C.c_void_p * ring)()
+        for r in range(ring):
+            f = dev.DeviceFrame16(full)
+            b = dev.DeviceBuffer(w * h * 4)
+            keep += [f, b]
+            outs[r], bufs[r] = f.c, b.ptr.value
+        targets[g].out, targets[g].ring = outs, ring
+        u8_rings.append(bufs)
+        table = dev.display_table(1.25)
+        targets[g].u8_table = table
+        host = PinnedArray(dev, (ring, h, w, 4), np.uint8)
+        pinned_out.append(host)
+        keep += [outs, bufs, table, host]
+    dev.init(B.local)
+
+    counters = [0] * n_gpus
+
+    @A.TIMELINE_SINK
+    def sink(user, slot, frame, job, stream):
+        k = counters[slot] % ring
+        counters[slot] += 1
+        return lib.cv_download(C.c_void_p(pinned_out[slot].ptr.value + k * w * h * 4), job.contents.out_u8, w * h * 4, stream)
+
+    coverage = sum((b[2] - b[0] + 1) * (b[3] - b[1] + 1) for b in windows)
+    result = {"n_gpus": n_gpus, "frames": frames, "chunk": chunk, "ring": ring, "workload": "4k_timeline_windows (BASELINE.json configs[4])"}
+    for mode in ("resident", "pulled_u8"):
+        items = make_items(mode == "pulled_u8")
+        run = A.TimelineRun()
+        run.items, run.item_count, run.n_gpus = items, 4, n_gpus
+        run.first, run.last, run.chunk, run.targets = 0, frames - 1, chunk, targets
+        for g in range(n_gpus):             # the 8-bit targets exist only in the end-to-end mode
+            targets[g].out_u8 = C.cast(u8_rings[g], C.POINTER(C.c_void_p)) if mode == "pulled_u8" else None
+        if mode == "pulled_u8":
+            run.sink = sink
+        stats = (A.TimelineStats * n_gpus)()
+        warm = A.TimelineRun()
+        C.memmove(C.byref(warm), C.byref(run), C.sizeof(run))
+        warm.last = min(frames, 4 * chunk * n_gpus) - 1
+        dev.check(lib.cv_timeline_render(C.byref(warm), stats), "cv_timeline_render (warm-up)")
+        before = lib.cv_kernel_launches()
+        t0 = time.perf_counter()
+        dev.check(lib.cv_timeline_render(C.byref(run), stats), "cv_timeline_render")
+        wall = time.perf_counter() - t0
+        device_ms = max(s.device_ms for s in stats)
+        bytes_per_frame = 4 * w * h + 8 * coverage + 8 * w * h + (4 * w * h if mode == "pulled_u8" else 0)
+        result[mode] = {"value": frames / wall, "unit": "frames/s", "wall_ms": wall * 1e3, "slowest_gpu_device_ms": device_ms,
+                        "device_fps": frames / (device_ms * 1e-3), "gpu_launches": int(lib.cv_kernel_launches() - before),
+                        "frames_per_gpu": [int(s.frames) for s in stats], "algorithmic_gb_per_s": bytes_per_frame * frames / wall / 1e9,
+                        "h2d_bytes_per_frame": (sum(int(s.h2d_bytes) for s in stats) / frames), "d2h_bytes_per_frame": (4 * w * h if mode == "pulled_u8" else 0)}
+    for k in keep:
+        if hasattr(k, "free"):
+            try:
+                k.free()
+            except Exception:
+                pass
+    return result
+
+
 def run_ours(args):
     B = Bench(args)
     dev, name = B.dev, args.workload
@@ -588,6 +780,8 @@ def run_ours(args):
         "gpu_launches": m["launches"], "clocks": m["clocks"],
     }
     line.update(parity)
+    if sets[0].host_layers and not sets[0].host_coded and sets[0].out_u8 is None and not args.no_plugin:
+        line["e2e_plugin"] = plugin_e2e(B, name, sets, check=not args.no_check)
     for s in sets:
         s.free()
     sets = None
@@ -611,6 +805,15 @@ def run_ours(args):
             for s in osets:
                 s.free()
         line["other_workloads"] = others
+
+    # ---- the frame-parallel scheduler itself: ONE cv_timeline_render() call over all the GPUs of the job -------------
+    if not args.no_scheduler:
+        B.barrier()                         # the other ranks idle from here on (their GPUs are driven by rank 0's workers)
+        if B.rank == 0:
+            n_sched = max(B.world, args.gpus if B.dist is None else B.world)
+            n_sched = min(n_sched, B.lib.cv_device_count())
+            line["scheduler"] = scheduler_bench(B, n_sched, frames=1000)
+        B.barrier()
 
     if B.rank == 0 and B.world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(name, seconds=20.0)
@@ -784,6 +987,8 @@ def main():
     ap.add_argument("--no-others", action="store_true", help="skip the other_workloads array")
     ap.add_argument("--no-check", action="store_true", help="skip the oracle comparison after the timed region")
     ap.add_argument("--no-numa", action="store_true", help="do not pin the process to the GPU's NUMA node")
+    ap.add_argument("--no-plugin", action="store_true", help="skip e2e_plugin (the framework.h pull with host frames)")
+    ap.add_argument("--no-scheduler", action="store_true", help="skip the cv_timeline_render() measurement over all GPUs")
     ap.add_argument("--planar", action="store_true", help="4:2:2 sources as three planes instead of packed UYVY")
     ap.add_argument("--content", default="noise", choices=["noise", "video"],
                     help="coded sources: independent random bytes (default) or smooth picture-like content")

@@ -16,6 +16,7 @@ CV_LAYOUT_PLANAR, CV_LAYOUT_UYVY, CV_LAYOUT_YUY2 = 0, 1, 2
 CV_MATRIX_709, CV_MATRIX_601 = 0, 1
 CV_SRC_NONE, CV_SRC_F16, CV_SRC_CODED, CV_SRC_F32 = 0, 1, 2, 3
 CV_MAX_LAYERS = 16
+CV_TIMELINE_STATIC = 1
 
 
 class CanvasError(RuntimeError):
@@ -96,11 +97,26 @@ class Clip(C.Structure):
     _fields_ = [("frames", C.POINTER(Source)), ("count", C.c_int32), ("reserved", C.c_int32)]
 
 
+class CodedImageSourceFuncs(C.Structure):
+    """coded_image_source_funcs (include/framework.h)"""
+    _fields_ = [("flags", C.c_int), ("getFrame", C.c_void_p)]
+
+
+class CodedImageSource(C.Structure):
+    """coded_image_source"""
+    _fields_ = [("obj", C.c_void_p), ("funcs", C.POINTER(CodedImageSourceFuncs))]
+
+
+class Pull(C.Structure):
+    """cv_pull: pictures pulled from the host while a timeline renders"""
+    _fields_ = [("coded", C.POINTER(CodedImageSource)), ("format", Coded), ("video", C.c_void_p), ("full_window", Box2i)]
+
+
 class TimelineItem(C.Structure):
     """cv_timeline_item"""
     _fields_ = [("x", C.c_int64), ("length", C.c_int64), ("z", C.c_int64), ("offset", C.c_int64),
                 ("clips", C.POINTER(Clip)), ("clips_b", C.POINTER(Clip)), ("mix_first", C.c_float), ("mix_last", C.c_float),
-                ("ramp_start", C.c_int64), ("ramp_length", C.c_int64)]
+                ("ramp_start", C.c_int64), ("ramp_length", C.c_int64), ("pull", C.POINTER(Pull)), ("pull_b", C.POINTER(Pull))]
 
 
 class TimelineTarget(C.Structure):
@@ -116,13 +132,13 @@ class TimelineRun(C.Structure):
     """cv_timeline_run"""
     _fields_ = [("items", C.POINTER(TimelineItem)), ("item_count", C.c_int32), ("n_gpus", C.c_int32),
                 ("devices", C.POINTER(C.c_int32)), ("first", C.c_int64), ("last", C.c_int64), ("chunk", C.c_int32),
-                ("reserved", C.c_int32), ("targets", C.POINTER(TimelineTarget)), ("sink", TIMELINE_SINK), ("user", C.c_void_p)]
+                ("flags", C.c_int32), ("targets", C.POINTER(TimelineTarget)), ("sink", TIMELINE_SINK), ("user", C.c_void_p)]
 
 
 class TimelineStats(C.Structure):
     """cv_timeline_stats"""
     _fields_ = [("device", C.c_int32), ("reserved", C.c_int32), ("frames", C.c_int64), ("launches", C.c_uint64),
-                ("device_ms", C.c_double), ("wall_ms", C.c_double)]
+                ("device_ms", C.c_double), ("wall_ms", C.c_double), ("h2d_bytes", C.c_uint64)]
 
 
 _PROTOTYPES = {
@@ -146,6 +162,7 @@ _PROTOTYPES = {
     "cv_event_elapsed_ms": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_float)]),
     "cv_malloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t, C.c_int]),
     "cv_free": (C.c_int, [C.c_void_p, C.c_int]),
+    "cv_free_async": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "cv_memset": (C.c_int, [C.c_void_p, C.c_int, C.c_size_t, C.c_void_p]),
     "cv_upload": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "cv_download": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),

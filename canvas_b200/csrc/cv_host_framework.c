@@ -4,7 +4,10 @@
  * callers and for the fluggo.media.process extension: same symbols, same argument meaning, same
  * "empty current_window on failure" convention, but every pixel is produced by the sm_100a
  * kernels.  Frames passed here hold HOST pointers (as in the reference); they are moved to HBM,
- * processed and moved back.  Callers that can keep frames resident use include/canvas_b200.h.
+ * processed and moved back on the CALLING THREAD's own stream (cv_host_ctx.c), so concurrent callers never
+ * queue behind each other; frames this file pulls from a source are produced straight into pinned staging
+ * slabs (true asynchronous DMA), frames handed in by the caller are copied from wherever they live (the
+ * CUDA driver stages pageable memory itself).  Callers that can keep frames resident use include/canvas_b200.h.
  *
  * Replaces (paths relative to /root/reference/src/cprocess):
  *   half.c:87-105 (function-pointer binding), main.c:24-145 (time helpers, video_get_frame_*),
@@ -22,23 +25,21 @@
 
 /* ------------------------------------------------------------------ bring-up */
 
-static int host_ready( void ) {
-    if( cv_get_device() >= 0 )
-        return 1;
-
-    const char *env = getenv( "CANVAS_B200_DEVICE" );
-    const int rc = cv_init( env ? atoi( env ) : 0 );
-
-    if( rc != CV_OK ) {
+/* the calling thread's stream (and through it the device), or NULL when no B200 can be used */
+static CvHostCtx *host_ctx( void ) {
+    CvHostCtx *ctx = cvi_host_ctx();
+    if( !ctx ) {
         static int warned;
         if( !warned ) {
             warned = 1;
             fprintf( stderr, "canvas_b200: %s\n", cv_last_error() );
         }
-        return 0;
     }
-    return 1;
+    return ctx;
 }
+
+static int host_ready( void ) { return host_ctx() != NULL; }
+static cv_stream host_stream( void ) { CvHostCtx *ctx = cvi_host_ctx(); return ctx ? (cv_stream) ctx->stream : NULL; }
 
 /* device scratch for one host<->device round trip */
 typedef struct Scratch { void *dev; size_t bytes; } Scratch;
@@ -48,23 +49,22 @@ static int scratch_up( Scratch *s, const void *host, size_t bytes ) {
     s->bytes = bytes;
     int rc = cv_malloc( &s->dev, bytes ? bytes : 1, CV_MEM_DEVICE );
     if( !rc && host && bytes )
-        rc = cv_upload( s->dev, host, bytes, NULL );
+        rc = cv_upload( s->dev, host, bytes, host_stream() );
     return rc;
 }
 
 static int scratch_down( Scratch *s, void *host ) {
     int rc = CV_OK;
     if( host && s->bytes )
-        rc = cv_download( host, s->dev, s->bytes, NULL );
+        rc = cv_download( host, s->dev, s->bytes, host_stream() );
     if( !rc )
-        rc = cv_stream_sync( NULL );
+        rc = cv_stream_sync( host_stream() );
     return rc;
 }
 
 static void scratch_free( Scratch *s ) {
     if( s->dev ) {
-        cv_stream_sync( NULL );
-        cv_free( s->dev, CV_MEM_DEVICE );
+        cv_free_async( s->dev, CV_MEM_DEVICE, host_stream() );
         s->dev = NULL;
     }
 }
@@ -81,7 +81,7 @@ static void gpu_half_from_float( half *out, const float *in, int count ) {
     if( count <= 0 || !host_ready() ) return;
     Scratch src = { 0 }, dst = { 0 };
     if( !scratch_up( &src, in, sizeof(float) * (size_t) count ) && !scratch_up( &dst, NULL, sizeof(half) * (size_t) count ) &&
-            !cv_half_from_float( (half *) dst.dev, (const float *) src.dev, (size_t) count, NULL ) )
+            !cv_half_from_float( (half *) dst.dev, (const float *) src.dev, (size_t) count, host_stream() ) )
         scratch_down( &dst, out );
     scratch_free( &src );
     scratch_free( &dst );
@@ -91,7 +91,7 @@ static void gpu_half_to_float( float *out, const half *in, int count ) {
     if( count <= 0 || !host_ready() ) return;
     Scratch src = { 0 }, dst = { 0 };
     if( !scratch_up( &src, in, sizeof(half) * (size_t) count ) && !scratch_up( &dst, NULL, sizeof(float) * (size_t) count ) &&
-            !cv_half_to_float( (float *) dst.dev, (const half *) src.dev, (size_t) count, NULL ) )
+            !cv_half_to_float( (float *) dst.dev, (const half *) src.dev, (size_t) count, host_stream() ) )
         scratch_down( &dst, out );
     scratch_free( &src );
     scratch_free( &dst );
@@ -101,7 +101,7 @@ static void gpu_half_lookup( const half *table, half *out, const half *in, int c
     if( count <= 0 || !host_ready() ) return;
     Scratch tab = { 0 }, buf = { 0 };
     if( !scratch_up( &tab, table, sizeof(half) * HALF_COUNT ) && !scratch_up( &buf, in, sizeof(half) * (size_t) count ) &&
-            !cv_half_lookup( (const half *) tab.dev, (half *) buf.dev, (const half *) buf.dev, (size_t) count, NULL ) )
+            !cv_half_lookup( (const half *) tab.dev, (half *) buf.dev, (const half *) buf.dev, (size_t) count, host_stream() ) )
         scratch_down( &buf, out );
     scratch_free( &tab );
     scratch_free( &buf );
@@ -128,7 +128,7 @@ void init_half( void ) {
 static void transfer( int which, half *out, const half *in, size_t count ) {
     if( !count || !host_ready() ) return;
     Scratch buf = { 0 };
-    if( !scratch_up( &buf, in, sizeof(half) * count ) && !cv_transfer( which, (half *) buf.dev, (const half *) buf.dev, count, NULL ) )
+    if( !scratch_up( &buf, in, sizeof(half) * count ) && !cv_transfer( which, (half *) buf.dev, (const half *) buf.dev, count, host_stream() ) )
         scratch_down( &buf, out );
     scratch_free( &buf );
 }
@@ -242,7 +242,7 @@ static int copy_window( void *dst, const void *src, const box2i *full, const box
     const size_t pitch = (size_t) size.x * px;
     const size_t offset = ((size_t)(win->min.y - full->min.y) * (size_t) size.x + (size_t)(win->min.x - full->min.x)) * px;
     return cvi_cuda( cudaMemcpy2DAsync( (char *) dst + offset, pitch, (const char *) src + offset, pitch,
-        (size_t) wsize.x * px, (size_t) wsize.y, kind, cvi_stream( NULL ) ), "cudaMemcpy2DAsync(window)" );
+        (size_t) wsize.x * px, (size_t) wsize.y, kind, cvi_stream( host_stream() ) ), "cudaMemcpy2DAsync(window)" );
 }
 
 /* A device twin of a host f16/f32 frame: same windows, pooled HBM, the valid pixels uploaded. */
@@ -265,23 +265,23 @@ static int twin_f32( rgba_frame_f32 *dev, const rgba_frame_f32 *host, int upload
 }
 
 static void release_f16( rgba_frame_f16 *dev ) {
-    if( dev->data ) { cv_stream_sync( NULL ); cv_frame_free_f16( dev, CV_MEM_DEVICE ); }
+    if( dev->data ) { cv_free_async( dev->data, CV_MEM_DEVICE, host_stream() ); dev->data = NULL; }
 }
 static void release_f32( rgba_frame_f32 *dev ) {
-    if( dev->data ) { cv_stream_sync( NULL ); cv_frame_free_f32( dev, CV_MEM_DEVICE ); }
+    if( dev->data ) { cv_free_async( dev->data, CV_MEM_DEVICE, host_stream() ); dev->data = NULL; }
 }
 
 /* result window + its pixels back into the caller's frame */
 static int fetch_back_f16( rgba_frame_f16 *host, const rgba_frame_f16 *dev ) {
     host->current_window = dev->current_window;
     int rc = copy_window( host->data, dev->data, &host->full_window, &dev->current_window, sizeof(rgba_f16), cudaMemcpyDeviceToHost );
-    if( !rc ) rc = cv_stream_sync( NULL );
+    if( !rc ) rc = cv_stream_sync( host_stream() );
     return rc;
 }
 static int fetch_back_f32( rgba_frame_f32 *host, const rgba_frame_f32 *dev ) {
     host->current_window = dev->current_window;
     int rc = copy_window( host->data, dev->data, &host->full_window, &dev->current_window, sizeof(rgba_f32), cudaMemcpyDeviceToHost );
-    if( !rc ) rc = cv_stream_sync( NULL );
+    if( !rc ) rc = cv_stream_sync( host_stream() );
     return rc;
 }
 
@@ -304,9 +304,11 @@ void video_get_frame_f16( video_source *source, int frame_index, rgba_frame_f16 
         return;
     }
 
-    /* main.c:44-72: pull as f32 into a temporary of the same window, then pack (truncating) */
+    /* main.c:44-72: pull as f32 into a temporary of the same window (a pinned staging slab), then pack (truncating) */
+    CvHostCtx *ctx = host_ctx();
+    int slab = -1;
     rgba_frame_f32 temp;
-    temp.data = (rgba_f32 *) malloc( sizeof(rgba_f32) * (window_pixels( &frame->full_window ) + 1) );
+    temp.data = (rgba_f32 *) cvi_host_slab( ctx, sizeof(rgba_f32) * (window_pixels( &frame->full_window ) + 1), &slab );
     temp.full_window = frame->full_window;
     temp.current_window = frame->full_window;
     if( !temp.data ) { box2i_set_empty( &frame->current_window ); return; }
@@ -319,8 +321,9 @@ void video_get_frame_f16( video_source *source, int frame_index, rgba_frame_f16 
 
     if( !box2i_is_empty( &temp.current_window ) ) {
         rc = twin_f32( &dev32, &temp, 1 );
+        cvi_host_slab_done( ctx, slab );
         if( !rc ) rc = cv_frame_alloc_f16( &dev16, &frame->full_window, CV_MEM_DEVICE );
-        if( !rc ) rc = cv_frame_f32_to_f16( &dev16, &dev32, NULL );
+        if( !rc ) rc = cv_frame_f32_to_f16( &dev16, &dev32, host_stream() );
         if( !rc ) rc = fetch_back_f16( frame, &dev16 );
     }
 
@@ -331,7 +334,6 @@ void video_get_frame_f16( video_source *source, int frame_index, rgba_frame_f16 
 
     release_f32( &dev32 );
     release_f16( &dev16 );
-    free( temp.data );
 }
 
 void video_get_frame_f32( video_source *source, int frame_index, rgba_frame_f32 *frame ) {
@@ -350,9 +352,11 @@ void video_get_frame_f32( video_source *source, int frame_index, rgba_frame_f32 
         return;
     }
 
-    /* main.c:116-141: pull as f16, widen exactly */
+    /* main.c:116-141: pull as f16 (into a pinned staging slab), widen exactly */
+    CvHostCtx *ctx = host_ctx();
+    int slab = -1;
     rgba_frame_f16 temp;
-    temp.data = (rgba_f16 *) malloc( sizeof(rgba_f16) * (window_pixels( &frame->full_window ) + 1) );
+    temp.data = (rgba_f16 *) cvi_host_slab( ctx, sizeof(rgba_f16) * (window_pixels( &frame->full_window ) + 1), &slab );
     temp.full_window = frame->full_window;
     temp.current_window = frame->full_window;
     if( !temp.data ) { box2i_set_empty( &frame->current_window ); return; }
@@ -365,8 +369,9 @@ void video_get_frame_f32( video_source *source, int frame_index, rgba_frame_f32 
 
     if( !box2i_is_empty( &temp.current_window ) ) {
         rc = twin_f16( &dev16, &temp, 1 );
+        cvi_host_slab_done( ctx, slab );
         if( !rc ) rc = cv_frame_alloc_f32( &dev32, &frame->full_window, CV_MEM_DEVICE );
-        if( !rc ) rc = cv_frame_f16_to_f32( &dev32, &dev16, NULL );
+        if( !rc ) rc = cv_frame_f16_to_f32( &dev32, &dev16, host_stream() );
         if( !rc ) rc = fetch_back_f32( frame, &dev32 );
     }
 
@@ -377,7 +382,6 @@ void video_get_frame_f32( video_source *source, int frame_index, rgba_frame_f32 
 
     release_f16( &dev16 );
     release_f32( &dev32 );
-    free( temp.data );
 }
 
 /* ------------------------------------------------------------------ copies */
@@ -418,7 +422,7 @@ void video_copy_frame_alpha_f32( rgba_frame_f32 *out, rgba_frame_f32 *in, float 
     rgba_frame_f32 din = { 0 }, dout = { 0 };
     int rc = twin_f32( &din, in, 1 );
     if( !rc ) rc = cv_frame_alloc_f32( &dout, &out->full_window, CV_MEM_DEVICE );
-    if( !rc ) rc = cv_copy_frame_alpha_f32( &dout, &din, alpha, NULL );
+    if( !rc ) rc = cv_copy_frame_alpha_f32( &dout, &din, alpha, host_stream() );
     if( !rc ) rc = fetch_back_f32( out, &dout );
     if( rc ) box2i_set_empty( &out->current_window );
     release_f32( &din );
@@ -434,7 +438,7 @@ void video_mix_cross_f32( rgba_frame_f32 *out, rgba_frame_f32 *a, rgba_frame_f32
     int rc = twin_f32( &da, a, 1 );
     if( !rc ) rc = twin_f32( &db, b, 1 );
     if( !rc ) rc = cv_frame_alloc_f32( &dout, &out->full_window, CV_MEM_DEVICE );
-    if( !rc ) rc = cv_mix_cross_f32( &dout, &da, &db, mix_b, NULL );
+    if( !rc ) rc = cv_mix_cross_f32( &dout, &da, &db, mix_b, host_stream() );
     if( !rc ) rc = fetch_back_f32( out, &dout );
     if( rc ) box2i_set_empty( &out->current_window );
     release_f32( &da );
@@ -448,7 +452,7 @@ void video_mix_over_f32( rgba_frame_f32 *out, rgba_frame_f32 *b, float mix_b ) {
     rgba_frame_f32 dout = { 0 }, db = { 0 };
     int rc = twin_f32( &dout, out, 1 );
     if( !rc ) rc = twin_f32( &db, b, 1 );
-    if( !rc ) rc = cv_mix_over_f32( &dout, &db, mix_b, NULL );
+    if( !rc ) rc = cv_mix_over_f32( &dout, &db, mix_b, host_stream() );
     if( !rc ) rc = fetch_back_f32( out, &dout );
     if( rc ) box2i_set_empty( &out->current_window );
     release_f32( &dout );
@@ -482,13 +486,13 @@ void video_scale_bilinear_f32( rgba_frame_f32 *target, v2f target_point, rgba_fr
     rgba_frame_f32 dt = { 0 }, ds = { 0 };
     int rc = twin_f32( &dt, target, 0 );
     if( !rc ) rc = twin_f32( &ds, source, 1 );
-    if( !rc ) rc = cv_scale_bilinear_f32( &dt, target_point, &ds, source_point, factors, NULL );
+    if( !rc ) rc = cv_scale_bilinear_f32( &dt, target_point, &ds, source_point, factors, host_stream() );
     if( !rc ) {
         const int identity = factors.x == 1.0f && factors.y == 1.0f && target_point.x == source_point.x && target_point.y == source_point.y;
         target->current_window = dt.current_window;
         rc = copy_window( target->data, dt.data, &target->full_window, identity ? &dt.current_window : &target->full_window,
                           sizeof(rgba_f32), cudaMemcpyDeviceToHost );
-        if( !rc ) rc = cv_stream_sync( NULL );
+        if( !rc ) rc = cv_stream_sync( host_stream() );
     }
     if( rc ) box2i_set_empty( &target->current_window );
     release_f32( &dt );
@@ -531,7 +535,7 @@ static void color_in_place( rgba_frame_f16 *frame, int (*transform)( rgba_frame_
     rgba_frame_f16 dev = { 0 };
     const box2i keep = frame->current_window;
     int rc = twin_f16( &dev, frame, 1 );
-    if( !rc ) rc = transform( &dev, NULL );
+    if( !rc ) rc = transform( &dev, host_stream() );
     if( !rc ) rc = fetch_back_f16( frame, &dev );
     frame->current_window = keep;
     release_f16( &dev );
@@ -564,7 +568,7 @@ void video_reconstruct_dv( rgba_frame_f16 *frame, coded_image *planar ) {
 
     rgba_frame_f16 dev = { 0 };
     if( !rc ) rc = cv_frame_alloc_f16( &dev, &frame->full_window, CV_MEM_DEVICE );
-    if( !rc ) rc = cv_convert_ycbcr8( &dev, &image, NULL );
+    if( !rc ) rc = cv_convert_ycbcr8( &dev, &image, host_stream() );
     if( !rc ) rc = fetch_back_f16( frame, &dev );
     if( rc ) box2i_set_empty( &frame->current_window );
 
@@ -595,9 +599,9 @@ coded_image *video_subsample_dv( rgba_frame_f16 *frame ) {
 
     rgba_frame_f16 dev = { 0 };
     if( !rc ) rc = twin_f16( &dev, frame, 1 );
-    if( !rc ) rc = cv_subsample_ycbcr8( &dev, &image, NULL );
+    if( !rc ) rc = cv_subsample_ycbcr8( &dev, &image, host_stream() );
     for( int i = 0; i < 3 && !rc; i++ )
-        rc = cv_download( planar->data[i], plane[i].dev, (size_t) strides[i] * lines[i], NULL );
+        rc = cv_download( planar->data[i], plane[i].dev, (size_t) strides[i] * lines[i], host_stream() );
     if( !rc ) {
         const box2i keep = frame->current_window;
         rc = fetch_back_f16( frame, &dev );

@@ -6,11 +6,16 @@
  *
  *   - the reference keeps two sorted GSequences plus a moving "composite list" that is updated
  *     under a mutex as the playhead moves (:243-307), a sequential-access optimisation.  Here the
- *     set of items showing at a frame is a STATELESS query (x <= frame < x + length, ordered by z),
- *     so any number of threads / GPUs can render different frames of one workspace at once;
- *   - layers are accumulated in HBM: each source is pulled with the reference's own vtable
- *     (video_get_frame_f16/_f32), uploaded once, and the whole stack is composited by ONE fused
- *     launch when every source is f16-native, or by the f32 "over" kernel otherwise; one download.
+ *     set of items showing at a frame is a STATELESS query (x <= frame < x + length, ordered by z)
+ *     over an array sorted by x with a running maximum of the items' ends: a binary search finds the
+ *     last item that starts at or before the frame, and the walk back from it stops as soon as no
+ *     earlier item can still be showing -- O(log n + items near the frame), so any number of threads /
+ *     GPUs can render different frames of one 10 000-item workspace at once;
+ *   - layers are accumulated in HBM on the CALLING THREAD's own stream (cv_host_ctx.c): each source is
+ *     pulled with the reference's own vtable (video_get_frame_f16/_f32) straight into a pinned staging
+ *     slab, its valid rows go up as an asynchronous copy while the next source is being pulled, and the
+ *     whole stack is composited by ONE fused launch when every source is f16-native (the f32 "over"
+ *     kernel otherwise); one download.  Nothing here waits for another thread's work.
  *
  * Order of equal-z items: the later-added item is the lower one (what the reference build used by
  * the oracle does; the reference leaves it to GSequence's insertion order, so it is unpinned).
@@ -31,6 +36,7 @@ struct workspace_item_t_tag {
 struct workspace_t_tag {
     pthread_mutex_t lock;
     workspace_item_t **items;   /* kept sorted by (x, z) like the reference's leftsort (workspace_get_item order) */
+    int64_t *max_end;           /* max_end[i] = the largest x + length among items[0..i] */
     int count, capacity;
     uint64_t next_serial;
 };
@@ -48,28 +54,46 @@ static int by_depth( const void *pa, const void *pb ) {
     return a->serial > b->serial ? -1 : (a->serial < b->serial);
 }
 
+static void refresh_ends( workspace_t *ws, int from ) {
+    for( int i = from < 0 ? 0 : from; i < ws->count; i++ ) {
+        const int64_t end = ws->items[i]->x + ws->items[i]->length;
+        ws->max_end[i] = (i > 0 && ws->max_end[i - 1] > end) ? ws->max_end[i - 1] : end;
+    }
+}
+
+/* index of the first item that sorts after `item` (binary search) */
+static int upper_bound( const workspace_t *ws, const workspace_item_t *item ) {
+    int lo = 0, hi = ws->count;
+    while( lo < hi ) {
+        const int mid = lo + (hi - lo) / 2;
+        if( by_position( ws->items[mid], item ) <= 0 ) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
 static void insert_sorted( workspace_t *ws, workspace_item_t *item ) {
     if( ws->count == ws->capacity ) {
         ws->capacity = ws->capacity ? ws->capacity * 2 : 16;
         ws->items = (workspace_item_t **) realloc( ws->items, sizeof(*ws->items) * (size_t) ws->capacity );
+        ws->max_end = (int64_t *) realloc( ws->max_end, sizeof(*ws->max_end) * (size_t) ws->capacity );
     }
-    int at = ws->count;
-    while( at > 0 && by_position( item, ws->items[at - 1] ) < 0 ) {
-        ws->items[at] = ws->items[at - 1];
-        at--;
-    }
+    const int at = upper_bound( ws, item );
+    memmove( &ws->items[at + 1], &ws->items[at], sizeof(*ws->items) * (size_t)(ws->count - at) );
     ws->items[at] = item;
     ws->count++;
+    refresh_ends( ws, at );
 }
 
 static void detach( workspace_t *ws, workspace_item_t *item ) {
-    for( int i = 0; i < ws->count; i++ ) {
-        if( ws->items[i] == item ) {
-            memmove( &ws->items[i], &ws->items[i + 1], sizeof(*ws->items) * (size_t)(ws->count - i - 1) );
-            ws->count--;
-            return;
-        }
+    /* the item sits just before its own upper bound */
+    int at = upper_bound( ws, item ) - 1;
+    if( at < 0 || ws->items[at] != item ) {
+        for( at = 0; at < ws->count && ws->items[at] != item; at++ ) ;
+        if( at == ws->count ) return;
     }
+    memmove( &ws->items[at], &ws->items[at + 1], sizeof(*ws->items) * (size_t)(ws->count - at - 1) );
+    ws->count--;
+    refresh_ends( ws, at );
 }
 
 workspace_t *workspace_create( void ) {
@@ -118,6 +142,7 @@ void workspace_free( workspace_t *ws ) {
     for( int i = 0; i < ws->count; i++ )
         free( ws->items[i] );
     free( ws->items );
+    free( ws->max_end );
     pthread_mutex_destroy( &ws->lock );
     free( ws );
 }
@@ -147,6 +172,7 @@ void workspace_update_item( workspace_item_t *item, int64_t *x, int64_t *width, 
     if( source ) item->source = *source;
     if( tag ) item->tag = *tag;
     if( moves ) insert_sorted( ws, item );
+    else if( width ) refresh_ends( ws, 0 );
     pthread_mutex_unlock( &ws->lock );
 }
 
@@ -157,11 +183,19 @@ typedef struct Showing { video_source *source; int frame; } Showing;
 /* The items showing at `frame`, bottom first (workspace.c:510-520, 530, 542). */
 static int showing_at( workspace_t *ws, int frame, Showing **out ) {
     pthread_mutex_lock( &ws->lock );
-    workspace_item_t **hit = (workspace_item_t **) malloc( sizeof(*hit) * (size_t)(ws->count + 1) );
+
+    /* the last item with x <= frame, then back while an earlier item may still reach the frame */
+    int lo = 0, hi = ws->count;
+    while( lo < hi ) {
+        const int mid = lo + (hi - lo) / 2;
+        if( ws->items[mid]->x <= (int64_t) frame ) lo = mid + 1; else hi = mid;
+    }
+
+    workspace_item_t **hit = (workspace_item_t **) malloc( sizeof(*hit) * (size_t)(lo + 1) );
     int n = 0;
-    for( int i = 0; i < ws->count; i++ ) {
+    for( int i = lo - 1; i >= 0 && ws->max_end[i] > (int64_t) frame; i-- ) {
         workspace_item_t *it = ws->items[i];
-        if( it->x <= (int64_t) frame && (int64_t) frame < it->x + it->length )
+        if( (int64_t) frame < it->x + it->length )
             hit[n++] = it;
     }
     qsort( hit, (size_t) n, sizeof(*hit), by_depth );
@@ -190,107 +224,135 @@ static int all_f16_native( const Showing *list, int n ) {
     return 1;
 }
 
-/* Every showing source is f16-native: pull, upload the valid rows, ONE fused composite launch. */
-static int render_fused_f16( const Showing *list, int n, rgba_frame_f16 *frame ) {
+/* rows of `win` between a host buffer and a device buffer that both hold full_window, on the thread's stream */
+static int copy_rows( void *dst, const void *src, const box2i *full, const box2i *win, size_t px, enum cudaMemcpyKind kind, cudaStream_t stream ) {
+    if( box2i_is_empty( win ) ) return CV_OK;
+    v2i size, wsize;
+    box2i_get_size( full, &size );
+    box2i_get_size( win, &wsize );
+    const size_t pitch = (size_t) size.x * px;
+    const size_t offset = ((size_t)(win->min.y - full->min.y) * (size_t) size.x + (size_t)(win->min.x - full->min.x)) * px;
+    if( wsize.x == size.x )         /* whole rows: one contiguous copy */
+        return cvi_cuda( cudaMemcpyAsync( (char *) dst + offset, (const char *) src + offset, pitch * (size_t) wsize.y, kind, stream ), "cudaMemcpyAsync(rows)" );
+    return cvi_cuda( cudaMemcpy2DAsync( (char *) dst + offset, pitch, (const char *) src + offset, pitch,
+        (size_t) wsize.x * px, (size_t) wsize.y, kind, stream ), "cudaMemcpy2DAsync(window)" );
+}
+
+static void copy_window_to_caller( void *dst, const void *src, const box2i *full, const box2i *win, size_t px ) {
+    if( box2i_is_empty( win ) ) return;
+    v2i size, wsize;
+    box2i_get_size( full, &size );
+    box2i_get_size( win, &wsize );
+    for( int y = win->min.y; y <= win->max.y; y++ ) {
+        const size_t offset = ((size_t)(y - full->min.y) * (size_t) size.x + (size_t)(win->min.x - full->min.x)) * px;
+        memcpy( (char *) dst + offset, (const char *) src + offset, (size_t) wsize.x * px );
+    }
+}
+
+/* Every showing source is f16-native: pull each into a pinned slab, send its valid rows up asynchronously while the
+ * next one is pulled, ONE fused composite launch, one download. */
+static int render_fused_f16( CvHostCtx *ctx, const Showing *list, int n, rgba_frame_f16 *frame ) {
+    const size_t bytes = sizeof(rgba_f16) * window_pixels( &frame->full_window );
     cv_layer *layers = (cv_layer *) calloc( (size_t) n, sizeof(cv_layer) );
-    rgba_frame_f16 host;
-    host.data = (rgba_f16 *) malloc( sizeof(rgba_f16) * (window_pixels( &frame->full_window ) + 1) );
-    host.full_window = frame->full_window;
-    int rc = (layers && host.data) ? CV_OK : CV_ERR_MEMORY;
+    int rc = layers ? CV_OK : cvi_fail( CV_ERR_MEMORY, "out of host memory" );
 
     for( int i = 0; i < n && !rc; i++ ) {
+        int slab = -1;
+        rgba_frame_f16 host;
+        host.data = (rgba_f16 *) cvi_host_slab( ctx, bytes, &slab );
+        host.full_window = frame->full_window;
         host.current_window = frame->full_window;
+        if( !host.data ) { rc = CV_ERR_MEMORY; break; }
+
         video_get_frame_f16( list[i].source, list[i].frame, &host );
+
         rc = cv_frame_alloc_f16( &layers[i].frame, &frame->full_window, CV_MEM_DEVICE );
-        if( !rc ) rc = cv_frame_upload_f16( &layers[i].frame, &host, NULL );
-        if( !rc ) rc = cv_stream_sync( NULL );          /* `host` is reused for the next layer */
+        box2i_intersect( &layers[i].frame.current_window, &host.current_window, &frame->full_window );
+        if( !rc ) rc = copy_rows( layers[i].frame.data, host.data, &frame->full_window, &layers[i].frame.current_window,
+                                  sizeof(rgba_f16), cudaMemcpyHostToDevice, ctx->stream );
+        cvi_host_slab_done( ctx, slab );
         layers[i].mix = 1.0f;
     }
 
     rgba_frame_f16 out = { 0 };
     if( !rc ) rc = cv_frame_alloc_f16( &out, &frame->full_window, CV_MEM_DEVICE );
-    if( !rc ) rc = cv_composite_over_f16( &out, layers, n, NULL );
-    if( !rc ) rc = cv_frame_download_f16( &host, &out, NULL );
-    if( !rc ) rc = cv_stream_sync( NULL );
+    if( !rc ) rc = cv_composite_over_f16( &out, layers, n, (cv_stream) ctx->stream );
 
     if( !rc ) {
-        /* only the result window is written into the caller's frame */
-        frame->current_window = out.current_window;
-        if( !box2i_is_empty( &out.current_window ) ) {
-            v2i size;
-            box2i_get_size( &out.current_window, &size );
-            for( int y = out.current_window.min.y; y <= out.current_window.max.y; y++ )
-                memcpy( video_get_pixel_f16( frame, out.current_window.min.x, y ), video_get_pixel_f16( &host, out.current_window.min.x, y ),
-                    sizeof(rgba_f16) * (size_t) size.x );
+        int slab = -1;
+        void *staging = cvi_host_slab( ctx, bytes, &slab );
+        if( !staging ) rc = CV_ERR_MEMORY;
+        if( !rc ) rc = copy_rows( staging, out.data, &frame->full_window, &out.current_window, sizeof(rgba_f16), cudaMemcpyDeviceToHost, ctx->stream );
+        if( !rc ) rc = cvi_cuda( cudaStreamSynchronize( ctx->stream ), "cudaStreamSynchronize" );
+        if( !rc ) {
+            /* only the result window is written into the caller's frame */
+            frame->current_window = out.current_window;
+            copy_window_to_caller( frame->data, staging, &frame->full_window, &out.current_window, sizeof(rgba_f16) );
         }
     }
 
-    cv_stream_sync( NULL );
     for( int i = 0; i < n; i++ )
-        if( layers && layers[i].frame.data ) cv_frame_free_f16( &layers[i].frame, CV_MEM_DEVICE );
-    if( out.data ) cv_frame_free_f16( &out, CV_MEM_DEVICE );
+        if( layers && layers[i].frame.data ) { cvi_pool_free_async( layers[i].frame.data, ctx->stream ); layers[i].frame.data = NULL; }
+    if( out.data ) cvi_pool_free_async( out.data, ctx->stream );
     free( layers );
-    free( host.data );
     return rc;
 }
 
-/* The general case (some source is f32-only): accumulate in an f32 frame in HBM. */
-static int render_accumulate_f32( const Showing *list, int n, rgba_frame_f32 *frame ) {
-    rgba_frame_f32 host, acc = { 0 }, layer = { 0 };
-    host.data = (rgba_f32 *) malloc( sizeof(rgba_f32) * (window_pixels( &frame->full_window ) + 1) );
-    host.full_window = frame->full_window;
-    int rc = host.data ? CV_OK : CV_ERR_MEMORY;
-
-    if( !rc ) rc = cv_frame_alloc_f32( &acc, &frame->full_window, CV_MEM_DEVICE );
-    if( !rc ) rc = cv_frame_alloc_f32( &layer, &frame->full_window, CV_MEM_DEVICE );
+/* The general case (some source is f32-only): accumulate in an f32 frame in HBM, two layer buffers in turn so that the
+ * upload of one layer overlaps the "over" of the previous one. */
+static int render_accumulate_f32( CvHostCtx *ctx, const Showing *list, int n, rgba_frame_f32 *frame, int into_caller, rgba_frame_f32 *keep_on_device ) {
+    const size_t bytes = sizeof(rgba_f32) * window_pixels( &frame->full_window );
+    rgba_frame_f32 acc = { 0 }, layer[2] = { { 0 }, { 0 } };
+    int rc = cv_frame_alloc_f32( &acc, &frame->full_window, CV_MEM_DEVICE );
+    if( !rc && n > 1 ) rc = cv_frame_alloc_f32( &layer[0], &frame->full_window, CV_MEM_DEVICE );
+    if( !rc && n > 2 ) rc = cv_frame_alloc_f32( &layer[1], &frame->full_window, CV_MEM_DEVICE );
 
     for( int i = 0; i < n && !rc; i++ ) {
+        int slab = -1;
+        rgba_frame_f32 host;
+        host.data = (rgba_f32 *) cvi_host_slab( ctx, bytes, &slab );
+        host.full_window = frame->full_window;
         host.current_window = frame->full_window;
+        if( !host.data ) { rc = CV_ERR_MEMORY; break; }
+
         video_get_frame_f32( list[i].source, list[i].frame, &host );
-        rgba_frame_f32 *target = (i == 0) ? &acc : &layer;
-        rc = cv_frame_upload_f32( target, &host, NULL );
-        if( !rc ) box2i_intersect( &target->current_window, &host.current_window, &frame->full_window );
-        if( !rc && i > 0 ) rc = cv_mix_over_f32( &acc, &layer, 1.0f, NULL );
-        if( !rc ) rc = cv_stream_sync( NULL );
+
+        rgba_frame_f32 *target = (i == 0) ? &acc : &layer[(i - 1) & 1];
+        box2i_intersect( &target->current_window, &host.current_window, &frame->full_window );
+        rc = copy_rows( target->data, host.data, &frame->full_window, &target->current_window, sizeof(rgba_f32), cudaMemcpyHostToDevice, ctx->stream );
+        cvi_host_slab_done( ctx, slab );
+        if( !rc && i > 0 ) rc = cv_mix_over_f32( &acc, target, 1.0f, (cv_stream) ctx->stream );
     }
 
-    if( !rc ) rc = cv_frame_download_f32( &host, &acc, NULL );
-    if( !rc ) rc = cv_stream_sync( NULL );
-
-    if( !rc ) {
-        frame->current_window = acc.current_window;
-        if( !box2i_is_empty( &acc.current_window ) ) {
-            v2i size;
-            box2i_get_size( &acc.current_window, &size );
-            for( int y = acc.current_window.min.y; y <= acc.current_window.max.y; y++ )
-                memcpy( video_get_pixel_f32( frame, acc.current_window.min.x, y ), video_get_pixel_f32( &host, acc.current_window.min.x, y ),
-                    sizeof(rgba_f32) * (size_t) size.x );
-        }
+    if( !rc && into_caller ) {
+        int slab = -1;
+        void *staging = cvi_host_slab( ctx, bytes, &slab );
+        if( !staging ) rc = CV_ERR_MEMORY;
+        if( !rc ) rc = copy_rows( staging, acc.data, &frame->full_window, &acc.current_window, sizeof(rgba_f32), cudaMemcpyDeviceToHost, ctx->stream );
+        if( !rc ) rc = cvi_cuda( cudaStreamSynchronize( ctx->stream ), "cudaStreamSynchronize" );
+        if( !rc ) copy_window_to_caller( frame->data, staging, &frame->full_window, &acc.current_window, sizeof(rgba_f32) );
     }
+    if( !rc ) frame->current_window = acc.current_window;
 
-    if( acc.data ) cv_frame_free_f32( &acc, CV_MEM_DEVICE );
-    if( layer.data ) cv_frame_free_f32( &layer, CV_MEM_DEVICE );
-    free( host.data );
+    if( layer[0].data ) cvi_pool_free_async( layer[0].data, ctx->stream );
+    if( layer[1].data ) cvi_pool_free_async( layer[1].data, ctx->stream );
+    if( !rc && keep_on_device ) *keep_on_device = acc;
+    else if( acc.data ) cvi_pool_free_async( acc.data, ctx->stream );
     return rc;
-}
-
-static int device_ready( void ) {
-    if( cv_get_device() >= 0 ) return 1;
-    const char *env = getenv( "CANVAS_B200_DEVICE" );
-    return cv_init( env ? atoi( env ) : 0 ) == CV_OK;
 }
 
 static void workspace_get_frame_f32( void *self, int frame_index, rgba_frame_f32 *frame ) {
     Showing *list = NULL;
     const int n = showing_at( (workspace_t *) self, frame_index, &list );
+    CvHostCtx *ctx = n ? cvi_host_ctx() : NULL;
 
-    if( n == 0 || !device_ready() ) {               /* workspace.c:504-508 */
+    if( n == 0 || !ctx ) {                          /* workspace.c:504-508 */
         box2i_set_empty( &frame->current_window );
         free( list );
         return;
     }
 
-    if( render_accumulate_f32( list, n, frame ) )
+    if( render_accumulate_f32( ctx, list, n, frame, 1, NULL ) )
         box2i_set_empty( &frame->current_window );
     free( list );
 }
@@ -298,8 +360,9 @@ static void workspace_get_frame_f32( void *self, int frame_index, rgba_frame_f32
 static void workspace_get_frame_f16( void *self, int frame_index, rgba_frame_f16 *frame ) {
     Showing *list = NULL;
     const int n = showing_at( (workspace_t *) self, frame_index, &list );
+    CvHostCtx *ctx = n ? cvi_host_ctx() : NULL;
 
-    if( n == 0 || !device_ready() ) {
+    if( n == 0 || !ctx ) {
         box2i_set_empty( &frame->current_window );
         free( list );
         return;
@@ -307,44 +370,36 @@ static void workspace_get_frame_f16( void *self, int frame_index, rgba_frame_f16
 
     int rc;
     if( all_f16_native( list, n ) ) {
-        rc = render_fused_f16( list, n, frame );
+        rc = render_fused_f16( ctx, list, n, frame );
     }
     else {
-        /* as the reference's dispatcher would: composite in f32, pack once at the end (main.c:44-72) */
-        rgba_frame_f32 wide, dev32 = { 0 };
+        /* as the reference's dispatcher would: composite in f32, pack once at the end (main.c:44-72) -- the f32 result
+         * stays in HBM and only the packed halves travel back */
+        rgba_frame_f32 wide = { 0 }, acc = { 0 };
         rgba_frame_f16 dev16 = { 0 };
-        wide.data = (rgba_f32 *) malloc( sizeof(rgba_f32) * (window_pixels( &frame->full_window ) + 1) );
         wide.full_window = frame->full_window;
-        rc = wide.data ? render_accumulate_f32( list, n, &wide ) : CV_ERR_MEMORY;
+        rc = render_accumulate_f32( ctx, list, n, &wide, 0, &acc );
 
-        if( !rc && !box2i_is_empty( &wide.current_window ) ) {
-            rgba_frame_f16 host;
-            host.data = (rgba_f16 *) malloc( sizeof(rgba_f16) * (window_pixels( &frame->full_window ) + 1) );
-            host.full_window = frame->full_window;
-            rc = cv_frame_alloc_f32( &dev32, &frame->full_window, CV_MEM_DEVICE );
-            if( !rc ) rc = cv_frame_upload_f32( &dev32, &wide, NULL );
+        if( !rc && !box2i_is_empty( &acc.current_window ) ) {
+            const size_t bytes = sizeof(rgba_f16) * window_pixels( &frame->full_window );
+            int slab = -1;
+            void *staging = cvi_host_slab( ctx, bytes, &slab );
+            if( !staging ) rc = CV_ERR_MEMORY;
             if( !rc ) rc = cv_frame_alloc_f16( &dev16, &frame->full_window, CV_MEM_DEVICE );
-            if( !rc ) rc = cv_frame_f32_to_f16( &dev16, &dev32, NULL );
-            if( !rc && host.data ) rc = cv_frame_download_f16( &host, &dev16, NULL );
-            if( !rc ) rc = cv_stream_sync( NULL );
-            if( !rc && host.data ) {
-                v2i size;
-                box2i_get_size( &dev16.current_window, &size );
-                for( int y = dev16.current_window.min.y; y <= dev16.current_window.max.y; y++ )
-                    memcpy( video_get_pixel_f16( frame, dev16.current_window.min.x, y ), video_get_pixel_f16( &host, dev16.current_window.min.x, y ),
-                        sizeof(rgba_f16) * (size_t) size.x );
+            if( !rc ) rc = cv_frame_f32_to_f16( &dev16, &acc, (cv_stream) ctx->stream );
+            if( !rc ) rc = copy_rows( staging, dev16.data, &frame->full_window, &dev16.current_window, sizeof(rgba_f16), cudaMemcpyDeviceToHost, ctx->stream );
+            if( !rc ) rc = cvi_cuda( cudaStreamSynchronize( ctx->stream ), "cudaStreamSynchronize" );
+            if( !rc ) {
+                copy_window_to_caller( frame->data, staging, &frame->full_window, &dev16.current_window, sizeof(rgba_f16) );
                 frame->current_window = dev16.current_window;
             }
-            free( host.data );
         }
         else if( !rc ) {
-            frame->current_window = wide.current_window;
+            frame->current_window = acc.current_window;
         }
 
-        cv_stream_sync( NULL );
-        if( dev32.data ) cv_frame_free_f32( &dev32, CV_MEM_DEVICE );
-        if( dev16.data ) cv_frame_free_f16( &dev16, CV_MEM_DEVICE );
-        free( wide.data );
+        if( acc.data ) cvi_pool_free_async( acc.data, ctx->stream );
+        if( dev16.data ) cvi_pool_free_async( dev16.data, ctx->stream );
     }
 
     if( rc )

@@ -190,9 +190,24 @@ int cvi_cuda( cudaError_t e, const char *what );    /* 0 or CV_ERR_CUDA */
 cudaStream_t cvi_stream( cv_stream s );
 void cvi_count_launch( unsigned n );
 
-/* pooled device allocations (cv_pool.cu) */
+/* pooled device allocations (cv_memory.c).  cvi_pool_free marks a block reusable at once (the caller has synchronised
+ * the work that used it); cvi_pool_free_async records an event behind the work queued on `stream` and the block is
+ * handed out again only after that event has completed. */
 int cvi_pool_alloc( void **ptr, size_t bytes );
 int cvi_pool_free( void *ptr );
+int cvi_pool_free_async( void *ptr, cudaStream_t stream );
+
+/* per-thread context of the framework.h entry points (cv_host_ctx.c): own stream, pinned staging slabs */
+enum { CV_HOST_SLABS = 4 };
+typedef struct CvHostCtx {
+    int device;
+    int next;
+    cudaStream_t stream;
+    struct { void *ptr; size_t bytes; cudaEvent_t done; int busy; } slab[CV_HOST_SLABS];
+} CvHostCtx;
+CvHostCtx *cvi_host_ctx( void );                                    /* NULL (error recorded) when no B200 can be initialised */
+void *cvi_host_slab( CvHostCtx *ctx, size_t bytes, int *index );    /* pinned staging memory; waits for the slab's previous copy */
+void cvi_host_slab_done( CvHostCtx *ctx, int index );               /* the slab's contents are in flight on ctx->stream */
 void cvi_pool_release_all( int device );
 
 /* kernels (cv_kernels.cu) */

@@ -12,7 +12,7 @@
 #include <stdlib.h>
 #include <string.h>
 
-typedef struct PoolBlock { void *ptr; size_t bytes; int in_use; } PoolBlock;
+typedef struct PoolBlock { void *ptr; size_t bytes; int in_use; int pending; cudaEvent_t event; } PoolBlock;
 
 typedef struct Pool {
     PoolBlock *blocks;
@@ -32,12 +32,27 @@ int cvi_pool_alloc( void **ptr, size_t bytes ) {
     Pool *pool = &g_pools[dev->index];
     pthread_mutex_lock( &dev->lock );
 
-    int best = -1;
+    /* the smallest fitting free block whose last user has finished; a block still waiting for its stream-ordered free
+     * (cvi_pool_free_async) is taken only when nothing else fits, and then waited for */
+    int best = -1, best_pending = -1;
     for( int i = 0; i < pool->count; i++ ) {
         PoolBlock *b = &pool->blocks[i];
-        if( !b->in_use && b->bytes >= bytes && b->bytes <= bytes + bytes / 4 &&
-                (best < 0 || b->bytes < pool->blocks[best].bytes) )
-            best = i;
+        if( b->in_use || b->bytes < bytes || b->bytes > bytes + bytes / 4 )
+            continue;
+        if( b->pending && cudaEventQuery( b->event ) == cudaSuccess )
+            b->pending = 0;
+        if( !b->pending ) {
+            if( best < 0 || b->bytes < pool->blocks[best].bytes ) best = i;
+        }
+        else if( best_pending < 0 || b->bytes < pool->blocks[best_pending].bytes )
+            best_pending = i;
+    }
+    cudaGetLastError();             /* cudaEventQuery reports cudaErrorNotReady through the sticky-free error slot */
+
+    if( best < 0 && best_pending >= 0 ) {
+        cudaEventSynchronize( pool->blocks[best_pending].event );
+        pool->blocks[best_pending].pending = 0;
+        best = best_pending;
     }
 
     if( best >= 0 ) {
@@ -55,6 +70,8 @@ int cvi_pool_alloc( void **ptr, size_t bytes ) {
         cudaGetLastError();
         for( int i = 0; i < pool->count; ) {
             if( !pool->blocks[i].in_use ) {
+                if( pool->blocks[i].pending ) cudaEventSynchronize( pool->blocks[i].event );
+                if( pool->blocks[i].event ) cudaEventDestroy( pool->blocks[i].event );
                 cudaFree( pool->blocks[i].ptr );
                 pool->blocks[i] = pool->blocks[--pool->count];
             }
@@ -76,6 +93,8 @@ int cvi_pool_alloc( void **ptr, size_t bytes ) {
     pool->blocks[pool->count].ptr = fresh;
     pool->blocks[pool->count].bytes = bytes;
     pool->blocks[pool->count].in_use = 1;
+    pool->blocks[pool->count].pending = 0;
+    pool->blocks[pool->count].event = NULL;
     pool->count++;
     *ptr = fresh;
     pthread_mutex_unlock( &dev->lock );
@@ -103,10 +122,42 @@ int cvi_pool_free( void *ptr ) {
     return rc;
 }
 
+int cvi_pool_free_async( void *ptr, cudaStream_t stream ) {
+    if( !ptr ) return CV_OK;
+    CvDevice *dev = cvi_device();
+    if( !dev ) return CV_ERR_NOT_INITIALISED;
+    Pool *pool = &g_pools[dev->index];
+    int rc = CV_ERR_ARGUMENT;
+
+    pthread_mutex_lock( &dev->lock );
+    for( int i = 0; i < pool->count; i++ ) {
+        PoolBlock *b = &pool->blocks[i];
+        if( b->ptr != ptr ) continue;
+        rc = CV_OK;
+        if( !b->event && cudaEventCreateWithFlags( &b->event, cudaEventDisableTiming ) != cudaSuccess )
+            b->event = NULL;
+        if( b->event && cudaEventRecord( b->event, stream ) == cudaSuccess )
+            b->pending = 1;
+        else {
+            cudaGetLastError();
+            cudaStreamSynchronize( stream );        /* no event: order the free by waiting */
+            b->pending = 0;
+        }
+        b->in_use = 0;
+        break;
+    }
+    pthread_mutex_unlock( &dev->lock );
+
+    if( rc ) return cvi_fail( rc, "cv pool: %p was not allocated by this device's pool", ptr );
+    return rc;
+}
+
 void cvi_pool_release_all( int device ) {
     Pool *pool = &g_pools[device];
-    for( int i = 0; i < pool->count; i++ )
+    for( int i = 0; i < pool->count; i++ ) {
+        if( pool->blocks[i].event ) cudaEventDestroy( pool->blocks[i].event );
         cudaFree( pool->blocks[i].ptr );
+    }
     free( pool->blocks );
     memset( pool, 0, sizeof(*pool) );
 }
@@ -126,6 +177,16 @@ int cv_free( void *ptr, int where ) {
     if( where == CV_MEM_PINNED )
         return cvi_cuda( cudaFreeHost( ptr ), "cudaFreeHost" );
     return cvi_pool_free( ptr );
+}
+
+int cv_free_async( void *ptr, int where, cv_stream stream ) {
+    if( !ptr ) return CV_OK;
+    if( where == CV_MEM_PINNED ) {
+        int rc = cv_stream_sync( stream );
+        return rc ? rc : cvi_cuda( cudaFreeHost( ptr ), "cudaFreeHost" );
+    }
+    if( !cvi_device() ) return CV_ERR_NOT_INITIALISED;
+    return cvi_pool_free_async( ptr, cvi_stream( stream ) );
 }
 
 int cv_memset( void *dev, int byte, size_t bytes, cv_stream stream ) {

@@ -38,6 +38,13 @@ def sync(stream=None):
     check(lib().cv_stream_sync(stream), "cv_stream_sync")
 
 
+def _quiesce():
+    """cv_free's contract (include/canvas_b200.h): the work that used a block has finished before the block goes back
+    to the pool.  These Python objects do not know which streams touched them (and __del__ runs whenever the collector
+    likes), so they wait for the whole device; code that frees on its own stream uses cv_free_async."""
+    lib().cv_device_sync()
+
+
 class DeviceFrame16:
     """An rgba_frame_f16 whose data pointer lives in HBM (cv_frame_alloc_f16)."""
 
@@ -82,6 +89,7 @@ class DeviceFrame16:
 
     def free(self):
         if self.c.data:
+            _quiesce()
             lib().cv_frame_free_f16(C.byref(self.c), CV_MEM_DEVICE)
 
     def __del__(self):
@@ -127,6 +135,7 @@ class DeviceFrame32:
 
     def free(self):
         if self.c.data:
+            _quiesce()
             lib().cv_frame_free_f32(C.byref(self.c), CV_MEM_DEVICE)
 
     def __del__(self):
@@ -165,6 +174,7 @@ class DeviceBuffer:
 
     def free(self):
         if self.ptr:
+            _quiesce()
             lib().cv_free(self.ptr, CV_MEM_DEVICE)
             self.ptr = C.c_void_p()
 

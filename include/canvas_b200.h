@@ -93,7 +93,11 @@ int cv_event_elapsed_ms( cv_event start, cv_event stop, float *ms );
 /* ------------------------------------------------------------------- memory */
 
 int cv_malloc( void **ptr, size_t bytes, int where /* CV_MEM_* */ );
+/* cv_free returns a device block to the pool at once: the caller must have synchronised every stream that used it.
+ * cv_free_async orders the free behind the work already queued on `stream` (the block is not handed out again before
+ * that work has finished) -- what a thread that renders on its own stream uses. */
 int cv_free( void *ptr, int where );
+int cv_free_async( void *ptr, int where, cv_stream stream );
 int cv_memset( void *dev, int byte, size_t bytes, cv_stream stream );
 int cv_upload( void *dev, const void *host, size_t bytes, cv_stream stream );      /* async when host is pinned */
 int cv_download( void *host, const void *dev, size_t bytes, cv_stream stream );
@@ -268,7 +272,8 @@ int cv_render_frames( cv_frame_job *jobs, int count, cv_stream stream );
  * The reference renders a timeline one frame at a time on one thread
  * (workspace_get_frame_f32, src/cprocess/workspace.c:494-550).  A frame depends only on its
  * index, so here a range of frames is partitioned over the GPUs of one box with no collective:
- * gpu slot = ((frame - first) / chunk) mod n_gpus, one host thread and one stream per GPU.
+ * chunks of consecutive frames go to whichever GPU is free next (or, with CV_TIMELINE_STATIC, to
+ * gpu slot = ((frame - first) / chunk) mod n_gpus), one host thread, a compute stream and a copy stream per GPU.
  *
  * A clip is a device-resident ring of sources (one ring PER GPU: frames are produced where their
  * inputs live); source frame i of a clip is frames[i mod count].
@@ -291,7 +296,29 @@ typedef struct {
     const cv_clip *clips_b;         /* [n_gpus] or NULL */
     float mix_first, mix_last;
     int64_t ramp_start, ramp_length;
+    const struct cv_pull_s *pull;   /* when set, `clips` is ignored: the item's pictures are pulled from the host (below) */
+    const struct cv_pull_s *pull_b; /* likewise for the crossfade's second source */
 } cv_timeline_item;
+
+/*
+ * Pictures PULLED from the host while the timeline renders, through the reference's own source interfaces:
+ *   coded   coded_image *getFrame( obj, source_frame, quality_hint 0 ) (include/framework.h:513-523; what
+ *           DVReconstructionFilter_get_frame calls per frame, src/process/DVReconstructionFilter.c:53-71).  The picture is
+ *           released with its own free_func once it has been copied.  `format` says what the planes hold (layout, width,
+ *           height, sub_x, matrix, pic_x / pic_y; its plane pointers are ignored, strides come from the coded_image);
+ *   video   a video_source pulled with video_get_frame_f16( source, source_frame, frame over full_window )
+ *           (src/cprocess/workspace.c:530-547 pulls every item this way).
+ * Exactly one of the two is set.  getFrame / get_frame are called on the GPU's worker thread (several GPUs call
+ * concurrently, as the reference's pull queue does).  Each worker stages what it pulls through its own ring of pinned
+ * buffers and a dedicated copy stream -- one cudaMemcpyAsync per plane, the kernels waiting on an event; memory that is
+ * already pinned (cv_malloc( ..., CV_MEM_PINNED ), cudaHostRegister) is copied from directly.
+ */
+typedef struct cv_pull_s {
+    coded_image_source *coded;
+    cv_coded format;
+    video_source *video;
+    box2i full_window;
+} cv_pull;
 
 /* Indices (into items) of the items showing at `frame`, bottom first; returns how many show. */
 int cv_timeline_showing( const cv_timeline_item *items, int count, int64_t frame, int *indices, int capacity );
@@ -326,8 +353,8 @@ typedef struct {
     int32_t n_gpus;
     const int32_t *devices;         /* [n_gpus] CUDA ordinals, or NULL for 0..n_gpus-1 */
     int64_t first, last;            /* inclusive */
-    int32_t chunk;                  /* consecutive frames per GPU turn (8..32 keeps input rings warm) */
-    int32_t reserved;
+    int32_t chunk;                  /* consecutive frames a GPU takes at a time (8..32 keeps input rings warm) */
+    int32_t flags;                  /* CV_TIMELINE_* */
     const cv_timeline_target *targets;  /* [n_gpus] */
     cv_timeline_sink sink;          /* may be NULL */
     void *user;
@@ -340,7 +367,13 @@ typedef struct {
     uint64_t launches;
     double device_ms;               /* CUDA events around this GPU's share, on its stream */
     double wall_ms;
+    uint64_t h2d_bytes;             /* what this GPU's worker pulled from the host (cv_pull items) */
 } cv_timeline_stats;
+
+/* By default a GPU that finishes its chunk takes the next undistributed one (a shared atomic counter: no GPU is left
+ * with a tail of frames while the others idle).  CV_TIMELINE_STATIC keeps the fixed block-cyclic deal of
+ * cv_timeline_device_of() -- frame -> GPU is then known in advance. */
+enum { CV_TIMELINE_STATIC = 1 };
 
 /* Renders frames first..last; blocks until every GPU has finished.  stats: [n_gpus] or NULL. */
 int cv_timeline_render( const cv_timeline_run *run, cv_timeline_stats *stats );

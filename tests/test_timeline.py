@@ -178,7 +178,26 @@ def test_two_rank_plumbing_over_gloo(tmp_path):
 
 # ----------------------------------------------------------------------------- GPU
 
-def _timeline_on_gpus(lib, n_gpus, ring=2, same_windows=False):
+def _client():
+    from canvas_b200 import _abi as A
+    client = C.CDLL(os.path.join(ROOT, "canvas_b200", "libcanvas_client.so"))
+    client.client_coded_clip_create.restype = C.c_void_p
+    client.client_coded_clip_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    client.client_coded_clip_source.restype = C.POINTER(A.CodedImageSource)
+    client.client_coded_clip_source.argtypes = [C.c_void_p]
+    client.client_coded_clip_pulls.restype = C.c_long
+    client.client_coded_clip_pulls.argtypes = [C.c_void_p]
+    client.client_coded_clip_free.argtypes = [C.c_void_p]
+    client.client_video_clip_create.restype = C.c_void_p
+    client.client_video_clip_create.argtypes = [C.POINTER(A.FrameF16), C.c_int]
+    client.client_video_clip_free.argtypes = [C.c_void_p]
+    return client
+
+
+def _timeline_on_gpus(lib, n_gpus, ring=2, same_windows=False, static=False, pull=False):
+    """static: the fixed block-cyclic deal (frame -> GPU known in advance); otherwise chunks are stolen.
+    pull: the two 4:2:2 clips come from the host through coded_image_source.getFrame (a: ordinary memory, staged through
+    the worker's pinned ring; b: pinned memory, copied from directly) and the first overlay through a video_source."""
     from canvas_b200 import _abi as A
     from canvas_b200 import device as dev
     w, h = 192, 64
@@ -192,7 +211,42 @@ def _timeline_on_gpus(lib, n_gpus, ring=2, same_windows=False):
     over2 = [O.synth_frame(full, 400 + i, (40 + (0 if same_windows else 2 * i), 0, w - 1, h - 1)) for i in range(4)]
 
     keep, clips = [], {}
+    pulls, client, coded_clips = {}, None, {}
+    if pull:
+        client = _client()
+        dev.init(0)
+        for name, pics in (("a", pics_a), ("b", pics_b)):
+            planes = (C.c_void_p * len(pics))()
+            for k, pic in enumerate(pics):
+                src = pic.planes[0]
+                if name == "b":                     # pinned: the scheduler copies straight out of it
+                    mem = C.c_void_p()
+                    dev.check(lib.cv_malloc(C.byref(mem), src.nbytes, A.CV_MEM_PINNED), "cv_malloc(pinned)")
+                    C.memmove(mem, src.ctypes.data, src.nbytes)
+                    planes[k] = mem.value
+                else:
+                    planes[k] = src.ctypes.data
+            stride, lines = (C.c_int * 1)(pics[0].planes[0].shape[1]), (C.c_int * 1)(h)
+            clip = client.client_coded_clip_create(planes, len(pics), 1, stride, lines)
+            coded_clips[name] = clip
+            p = A.Pull()
+            p.coded = client.client_coded_clip_source(clip)
+            p.format.layout, p.format.width, p.format.height = pics[0].layout, w, h
+            p.format.sub_x, p.format.matrix = 2, pics[0].matrix
+            pulls[name] = p
+            keep += [planes, stride, lines]
+        frames16 = (A.FrameF16 * len(over1))()
+        for k, hst in enumerate(over1):
+            frames16[k].data, frames16[k].full_window = hst.array.ctypes.data, A.Box2i(*hst.full.tuple())
+            frames16[k].current_window = A.Box2i(*hst.current.tuple())
+        p = A.Pull()
+        p.video = client.client_video_clip_create(frames16, len(over1))
+        p.full_window = A.Box2i(*full)
+        pulls["o1"] = p
+        keep.append(frames16)
     for name, hosts in (("a", pics_a), ("b", pics_b), ("o1", over1), ("o2", over2)):
+        if name in pulls:
+            continue
         arr = (A.Clip * n_gpus)()
         for g in range(n_gpus):
             dev.init(g)
@@ -211,10 +265,16 @@ def _timeline_on_gpus(lib, n_gpus, ring=2, same_windows=False):
 
     items = (A.TimelineItem * 3)()
     items[0].x, items[0].length, items[0].z, items[0].offset = 0, frames_total, 0, 1
-    items[0].clips, items[0].clips_b = clips["a"], clips["b"]
+    if pull:
+        items[0].pull, items[0].pull_b = C.pointer(pulls["a"]), C.pointer(pulls["b"])
+    else:
+        items[0].clips, items[0].clips_b = clips["a"], clips["b"]
     items[0].mix_first, items[0].mix_last, items[0].ramp_start, items[0].ramp_length = 0.0, 1.0, 1, frames_total - 1
     items[1].x, items[1].length, items[1].z, items[1].offset = 4, 12, 5, 0
-    items[1].clips = clips["o1"]
+    if pull:
+        items[1].pull = C.pointer(pulls["o1"])
+    else:
+        items[1].clips = clips["o1"]
     items[2].x, items[2].length, items[2].z, items[2].offset = 0, frames_total, 9, 3
     items[2].clips = clips["o2"]
 
@@ -243,6 +303,7 @@ def _timeline_on_gpus(lib, n_gpus, ring=2, same_windows=False):
     run.items, run.item_count, run.n_gpus = items, 3, n_gpus
     run.first, run.last, run.chunk = 0, frames_total - 1, chunk
     run.targets, run.sink = targets, sink
+    run.flags = A.CV_TIMELINE_STATIC if static else 0
     stats = (A.TimelineStats * n_gpus)()
     before = lib.cv_kernel_launches()
     dev.check(lib.cv_timeline_render(C.byref(run), stats), "cv_timeline_render")
@@ -253,13 +314,20 @@ def _timeline_on_gpus(lib, n_gpus, ring=2, same_windows=False):
         # frames, at most one extra launch per shape change
         assert lib.cv_kernel_launches() - before <= (frames_total + ring - 1) // ring + 4
     assert sum(s.frames for s in stats) == frames_total
-    assert [s.frames for s in stats] == [lib.cv_timeline_frames_of(g, 0, frames_total - 1, chunk, n_gpus) for g in range(n_gpus)]
+    if static:
+        assert [s.frames for s in stats] == [lib.cv_timeline_frames_of(g, 0, frames_total - 1, chunk, n_gpus) for g in range(n_gpus)]
     assert all(s.device_ms > 0 for s in stats if s.frames)
+    assert sorted(results) == list(range(frames_total))            # every frame exactly once, whoever rendered it
+    if pull:
+        # frames 0 and 22 short-circuit the crossfade (mix 0 / 1): one picture pulled there, two everywhere else
+        assert client.client_coded_clip_pulls(coded_clips["a"]) + client.client_coded_clip_pulls(coded_clips["b"]) >= 2 * frames_total - 2
+        assert sum(s.h2d_bytes for s in stats) >= (2 * frames_total - 2) * w * h * 2
 
     orc = O.oracle()
     for f in range(frames_total):
         slot, cw = results[f]
-        assert slot == lib.cv_timeline_device_of(f, 0, chunk, n_gpus)
+        if static:
+            assert slot == lib.cv_timeline_device_of(f, 0, chunk, n_gpus)
         src = f + 1
         t = (src - 1) / float(frames_total - 1)
         mix = float(np.float32(t)) if 0.0 < t < 1.0 else min(max(t, 0.0), 1.0)
@@ -279,6 +347,14 @@ def _timeline_on_gpus(lib, n_gpus, ring=2, same_windows=False):
 @pytest.mark.gpu
 def test_timeline_render_one_gpu(lib):
     _timeline_on_gpus(lib, 1)
+    _timeline_on_gpus(lib, 1, static=True)
+
+
+@pytest.mark.gpu
+def test_timeline_render_pulls_sources_from_the_host(lib):
+    """coded_image_source.getFrame and video_source pulls through the worker's pinned ring and copy stream"""
+    _timeline_on_gpus(lib, 1, ring=4, pull=True)
+    _timeline_on_gpus(lib, 1, ring=2, pull=True, static=True)
 
 
 @pytest.mark.gpu
@@ -293,4 +369,6 @@ def test_timeline_render_all_gpus(lib):
     if n < 2:
         pytest.skip("one GPU visible")
     _timeline_on_gpus(lib, min(n, 8))
+    _timeline_on_gpus(lib, min(n, 8), static=True)
     _timeline_on_gpus(lib, min(n, 8), ring=5, same_windows=True)
+    _timeline_on_gpus(lib, min(n, 8), ring=4, pull=True)
