@@ -23,9 +23,17 @@ import time
 
 import numpy as np
 
-from . import _abi, device as dev
+from . import _abi, _cbases, device as dev
 from ._abi import Box2i, check
 from .basetypes import box2i, rgba, v2i
+
+# The C base types of the CPython extension (fluggo.media.process, canvas_b200/csrc/py/py_process.c): they carry the
+# capsules C consumers bind to.  Plain Python bases when the extension has not been built.
+if _cbases.VideoSource is None:
+    _cbases.load()
+_VideoSourceBase = _cbases.VideoSource or object
+_CodedImageSourceBase = _cbases.CodedImageSource or object
+_FrameFunctionBase = _cbases.FrameFunction or object
 
 POINT_HOLD, POINT_LINEAR = 0, 1                  # AnimationFunc.c:23-24
 
@@ -55,8 +63,9 @@ def _clip(value, lo, hi):
 
 # ----------------------------------------------------------------------------- frame functions
 
-class FrameFunction:
-    """Base of the frame functions: get_values(frames) -> list of 4-tuples (FrameFunction.c / pyframework.h:69-74)."""
+class FrameFunction(_FrameFunctionBase):
+    """Base of the frame functions: get_values(frames) -> list of 4-tuples (FrameFunction.c / pyframework.h:69-74).
+    Derived from the extension's C type, so every frame function carries the `_frame_function_funcs` capsule."""
 
     def _values(self, frame):
         raise NotImplementedError
@@ -203,6 +212,8 @@ class _Holder:
             return
         if isinstance(source, FrameFunction) or hasattr(source, "get_values"):
             self.func = source
+        elif hasattr(source, "_frame_function_funcs") and _cbases.cmodule is not None:
+            self.func = _ForeignFrameFunction(source)           # another extension's function, through its capsule
         elif isinstance(source, box2i):
             self.constant = [float(v) for v in source.flat()]
         elif isinstance(source, tuple):
@@ -225,6 +236,18 @@ class _Holder:
 
     def rgba_f32(self, frame):
         return [float(np.float32(c)) for c in self.values(frame)]
+
+
+class _ForeignFrameFunction:
+    """A frame function that only offers the C interface (a `_frame_function_funcs` capsule, pyframework.h:69-93)."""
+
+    def __init__(self, obj):
+        self.obj = obj
+
+    def get_values(self, frames):
+        if isinstance(frames, (int, float)):
+            frames = [frames]
+        return _cbases.cmodule.framefunc_values(self.obj, [float(f) for f in frames])
 
 
 # ----------------------------------------------------------------------------- descriptions
@@ -310,11 +333,36 @@ def _cross_job(out, out_f32, a, b, mix, full, layers):
 
 # ----------------------------------------------------------------------------- frames
 
-class VideoSource:
-    """Base type: get_frame_f16 / get_frame_f32 (VideoSource.c:26-36)."""
+def _describe_of(source, frame_index, full):
+    """The description of ANY video source: one of this module's (its own _describe), or a foreign object that only
+    offers the C interface -- a `_video_frame_source_funcs` capsule (pyframework.h:52) -- which is pulled through its
+    vtable into host memory (py_video_take_source + video_get_frame_f16, GIL released) and sent to the device."""
+    if isinstance(source, VideoSource):
+        return source._describe(frame_index, full)
+    if _cbases.cmodule is None or not hasattr(source, "_video_frame_source_funcs"):
+        raise Exception("The source didn't have an acceptable _video_frame_source_funcs attribute.")
+    pixels, cw = _cbases.cmodule.pull_video_f16(source, int(frame_index), tuple(full))
+    if cw[2] < cw[0] or cw[3] < cw[1]:
+        return None
+    box = _box(full)
+    data = np.frombuffer(pixels, np.uint16).reshape(box.height, box.width, 4)
+    return _Desc("f16", dev.DeviceFrame16.from_numpy(data, box.flat(), cw))
+
+
+class VideoSource(_VideoSourceBase):
+    """Base type: get_frame_f16 / get_frame_f32 (VideoSource.c:26-36).  Derived from the extension's C type, so every
+    source carries the `_video_frame_source_funcs` capsule; _pull_f16 / _pull_f32 are what its vtable calls."""
 
     def _describe(self, frame_index, full):
         raise NotImplementedError
+
+    def _pull_f16(self, frame_index, window):
+        frame = self.get_frame_f16(frame_index, window)
+        return frame.data, frame.current_window.flat()
+
+    def _pull_f32(self, frame_index, window):
+        frame = self.get_frame_f32(frame_index, window)
+        return frame.data, frame.current_window.flat()
 
     def get_frame_f16(self, frame_index, data_window, force_gl=False):
         full = _flat(data_window)
@@ -452,7 +500,7 @@ class VideoPassThroughFilter(VideoSource):
                 return None
             if self._source is None:
                 return None
-            return self._source._describe(frame_index + self.offset, full)
+            return _describe_of(self._source, frame_index + self.offset, full)
 
 
 class VideoSequence(VideoSource):
@@ -497,7 +545,7 @@ class VideoSequence(VideoSource):
             start = 0
             for source, offset, length in self._elements:
                 if start <= frame_index < start + length:
-                    return source._describe(frame_index - start + offset, full) if source is not None else None
+                    return _describe_of(source, frame_index - start + offset, full) if source is not None else None
                 start += length
             return None                                             # before frame 0 or past the end (VideoSequence.c:59-83)
 
@@ -513,10 +561,10 @@ class VideoMixFilter(VideoSource):
         mix_b = _clip(self._mix.f32(frame_index), 0.0, 1.0)
         # video_mix_cross_f32_pull short-circuits the ends (video_mix.c:50-55)
         if mix_b == 0.0:
-            return self.src_a._describe(frame_index, full)
+            return _describe_of(self.src_a, frame_index, full)
         if mix_b == 1.0:
-            return self.src_b._describe(frame_index, full)
-        return _Desc("cross", a=self.src_a._describe(frame_index, full), b=self.src_b._describe(frame_index, full), mix=mix_b)
+            return _describe_of(self.src_b, frame_index, full)
+        return _Desc("cross", a=_describe_of(self.src_a, frame_index, full), b=_describe_of(self.src_b, frame_index, full), mix=mix_b)
 
 
 class VideoWorkspaceItem:
@@ -570,7 +618,7 @@ class VideoWorkspace(VideoSource):
         with self._lock:
             showing = [it for it in self._items if it.x <= frame_index < it.x + it.length]
             showing.sort(key=lambda it: (it.z, -it._serial))       # bottom first; later-added lower among equals
-            descs = [it.source._describe(frame_index - it.x + it.offset, full) if it.source is not None else None for it in showing]
+            descs = [_describe_of(it.source, frame_index - it.x + it.offset, full) if it.source is not None else None for it in showing]
         descs = [d for d in descs if d is not None]
         if not descs:
             return None
@@ -597,7 +645,7 @@ class VideoScaler(VideoSource):
         if fac[0] == 0.0 or fac[1] == 0.0:
             return None
         if fac == (1.0, 1.0) and tp == sp:
-            return self.source._describe(frame_index, full)
+            return _describe_of(self.source, frame_index, full)
         # the part of the source the target can see, computed with C's (int) truncation (video_scale.c:301-307)
         f32, trunc = np.float32, lambda v: int(np.trunc(v))
         want = box2i(trunc(f32(sp[0]) - (f32(tp[0]) - f32(full[0])) / f32(fac[0])) - 1,
@@ -608,7 +656,7 @@ class VideoScaler(VideoSource):
         if fetch[2] < fetch[0] or fetch[3] < fetch[1]:
             return None
         src = dev.DeviceFrame32(fetch)
-        _run(self.source._describe(frame_index, fetch), fetch, out_f32=src)
+        _run(_describe_of(self.source, frame_index, fetch), fetch, out_f32=src)
         out = dev.DeviceFrame32(full)
         V = _abi.V2f
         check(dev.lib().cv_scale_bilinear_f32(C.byref(out.c), V(*tp), C.byref(src.c), V(*sp), V(*fac), None), "cv_scale_bilinear_f32")
@@ -627,7 +675,7 @@ class VideoGainOffsetFilter(VideoSource):
         if self.source is None:
             return None
         frame = dev.DeviceFrame32(full)
-        _run(self.source._describe(frame_index, full), full, out_f32=frame)
+        _run(_describe_of(self.source, frame_index, full), full, out_f32=frame)
         if frame.current.empty:
             return None
         check(dev.lib().cv_gain_offset_f32(C.byref(frame.c), self._gain.f32(frame_index), self._offset.f32(frame_index), None),
@@ -648,14 +696,14 @@ class Pulldown23RemovalFilter(VideoSource):
         phase = (frame_index + 3) & 3 if self.offset == 4 else (frame_index + self.offset) & 3
         base = ((frame_index + self.offset) >> 2) * 5 - self.offset
         if phase != 2:
-            return self.source._describe(base + {0: 0, 1: 1, 3: 4}[phase], full)
+            return _describe_of(self.source, base + {0: 0, 1: 1, 3: 4}[phase], full)
         frame = dev.DeviceFrame16(full)
-        _run(self.source._describe(base + 2, full), full, out=frame)
+        _run(_describe_of(self.source, base + 2, full), full, out=frame)
         if frame.current.empty:
             return None
         window = frame.current.tuple()
         other = dev.DeviceFrame16(window)
-        _run(self.source._describe(base + 3, window), window, out=other)
+        _run(_describe_of(self.source, base + 3, window), window, out=other)
         # the reference copies those rows whatever the second frame defined; rows it did not define are left as they are
         check(dev.lib().cv_weave_fields_f16(C.byref(frame.c), C.byref(other.c), None), "cv_weave_fields_f16")
         return _Desc("f16", frame)
@@ -670,9 +718,30 @@ class CodedImage:
         self.data, self.stride, self.line_count = list(data), list(stride), list(line_count)
 
 
-class CodedImageSource:
+class CodedImageSource(_CodedImageSourceBase):
+    """Base of the coded image sources; carries the `_coded_image_source_funcs` capsule (pyframework.h:132), whose
+    getFrame calls _pull_coded."""
+
     def get_coded_image(self, frame):
         raise NotImplementedError
+
+    def _pull_coded(self, frame):
+        image = self.get_coded_image(frame)
+        if image is None:
+            return None
+        return [(bytes(d) if d is not None else b"", s, n) for d, s, n in zip(image.data, image.stride, image.line_count) if d is not None]
+
+
+def _coded_image_of(source, frame):
+    """source.get_coded_image(frame), or -- for a foreign source -- coded_image_source.getFrame through its capsule."""
+    if hasattr(source, "get_coded_image"):
+        return source.get_coded_image(frame)
+    if _cbases.cmodule is None or not hasattr(source, "_coded_image_source_funcs"):
+        raise Exception("The source didn't have an acceptable _coded_image_source_funcs attribute.")
+    planes = _cbases.cmodule.pull_coded(source, int(frame))
+    if planes is None:
+        return None
+    return CodedImage([p[0] for p in planes], [p[1] for p in planes], [p[2] for p in planes])
 
 
 _DV_WINDOW = (0, -1, 719, 478)                  # video_reconstruct.c:69-76, video_subsample.c:112-117
@@ -685,7 +754,7 @@ class DVReconstructionFilter(VideoSource):
         self.source = source
 
     def _describe(self, frame_index, full):
-        image = self.source.get_coded_image(frame_index) if self.source is not None else None
+        image = _coded_image_of(self.source, frame_index) if self.source is not None else None
         if image is None:
             return None
         widths = (720, 180, 180)
@@ -709,7 +778,7 @@ class DVSubsampleFilter(CodedImageSource):
 
     def get_coded_image(self, frame):
         out = dev.DeviceFrame16(_DV_WINDOW)
-        _run(self.source._describe(int(frame), _DV_WINDOW), _DV_WINDOW, out=out)
+        _run(_describe_of(self.source, int(frame), _DV_WINDOW), _DV_WINDOW, out=out)
         planes = [np.zeros((480, w), np.uint8) for w in (720, 180, 180)]
         coded = dev.DeviceCoded(planes, 720, 480, sub_x=4, layout=_abi.CV_LAYOUT_PLANAR, matrix=_abi.CV_MATRIX_709, pic=(0, -1), zero=True)
         dev.subsample_ycbcr8(out, coded)
@@ -728,7 +797,7 @@ class MPEG2SubsampleFilter(CodedImageSource):
 
     def get_coded_image(self, frame):
         out = dev.DeviceFrame16(self._WINDOW)
-        _run(self.source._describe(int(frame), self._WINDOW), self._WINDOW, out=out)
+        _run(_describe_of(self.source, int(frame), self._WINDOW), self._WINDOW, out=out)
         planes = [np.zeros((h, w), np.uint8) for w, h in ((720, 480), (360, 240), (360, 240))]
         coded = dev.DeviceCoded(planes, 720, 480, sub_x=2, layout=_abi.CV_LAYOUT_PLANAR, matrix=_abi.CV_MATRIX_601, pic=(0, 0), zero=True)
         dev.subsample_mpeg2(out, coded)
@@ -806,6 +875,15 @@ def time_get_frame(source, min_frame, max_frame, data_window=(0, 0, 1, 1)):
     dev.sync()
     start = time.perf_counter_ns()
     for frame in range(int(min_frame), int(max_frame) + 1):
-        _run(source._describe(frame, full), full, out=out)
+        _run(_describe_of(source, frame, full), full, out=out)
     dev.sync()
     return time.perf_counter_ns() - start
+
+
+# ----------------------------------------------------------------------------- fluggo.media.process
+# The extension module re-exports this module's public names (the reference's surface); done here, at the end, so that
+# it works whichever of the two modules was imported first.
+if _cbases.cmodule is not None:
+    for _name, _value in list(globals().items()):
+        if not _name.startswith("_") and _name not in ("np", "C", "dev", "bisect", "threading", "time"):
+            setattr(_cbases.cmodule, _name, _value)
