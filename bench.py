@@ -17,6 +17,7 @@ reported in the line's `other_workloads` array; `--workload NAME` makes any of t
                           bytes = 8 x (sum of layer window areas + output area) = 56.1 MB per frame)
     4k_timeline           2 x (4:2:2 -> f16) -> crossfade -> + 3 full-window overlays -> f16 (36 B/px)
     4k_timeline_windows   the same with PARTIAL overlay windows (configs[4]'s frame; 28.6 B/px)
+    4k_4layer_filters     4 full-window layers, three of them with per-pixel filters fused into the launch (40 B/px)
 
 A "step" renders enough frames to last about 50 ms (512 frames at 4K for the headline) with ONE
 cv_render_frames() call -- frames of one shape become persistent kernel launches of up to 256 frames; the plain
@@ -57,10 +58,14 @@ WORKLOADS = {
     "4k_timeline": (3840, 2160, 36, 640, "3840x2160 2x(4:2:2->f16) crossfade + 3 f16 overlays -> f16"),
     "4k_timeline_windows": (3840, 2160, None, 512, "3840x2160 2x(4:2:2->f16) crossfade + 3 f16 overlays with partial windows -> f16"),
     "1080p_4layer_windows": (1920, 1080, None, 3840, "1920x1080 4-layer alpha-over workspace composite, partial layer windows -> f16"),
+    "4k_4layer_filters": (3840, 2160, 40, 512, "3840x2160 4-layer composite, layers 1-3 with fused per-pixel filters (colour transform / gain+offset / crop) -> f16"),
 }
 # what the driver-run line reports next to the headline: BASELINE.json configs[0..4] and their variants
 OTHER_WORKLOADS = ["1080p_convert", "1080p_convert_planar", "1080p_cross_u8", "1080p_4layer_windows", "4k_composite_convert",
-                   "4k_convert", "4k_timeline", "4k_timeline_windows"]
+                   "4k_convert", "4k_timeline", "4k_timeline_windows", "4k_4layer_filters"]
+
+# the filters fused into layers 1..3 of 4k_4layer_filters (cv_layer_ops): flags, colour transform, gain, offset, crop
+LAYER_FILTERS = [None, (2, 1, 0.0, 0.0, None), (4, 0, 1.25, -0.03125, None), (4 | 8, 0, 0.75, 0.0625, (400, 200, 3400, 1900))]
 
 # layer windows of 1080p_4layer_windows (layer 0 covers the frame); inclusive corners
 WINDOWS_1080P = [(0, 0, 1919, 1079), (200, 100, 1719, 979), (480, 0, 1919, 700), (0, 540, 959, 1079)]
@@ -292,15 +297,37 @@ class InputSet:
             for i, window in enumerate(WINDOWS_1080P):
                 add_layer(i, window)
             self.job = dev.make_job(out=self.out, layers=self.layers)
+        elif name == "4k_4layer_filters":
+            for i in range(4):
+                add_layer(i)
+            self.job = dev.make_job(out=self.out, layers=self.layers)
+            self.layer_ops = self.attach_filters(self.job)
         else:
             raise SystemExit("unknown workload %r" % name)
 
         self.h2d_bytes = sum(p.nbytes for _, p in self.uploads)
         self.result = PinnedArray(dev, (self.d2h_bytes,), np.uint8) if pinned else None
 
+    def attach_filters(self, job):
+        """cv_layer.ops of the 4k_4layer_filters workload"""
+        A = self.dev._abi
+        ops = (A.LayerOps * len(LAYER_FILTERS))()
+        for i, spec in enumerate(LAYER_FILTERS):
+            if spec is None:
+                continue
+            ops[i].flags, ops[i].color, ops[i].gain, ops[i].offset = spec[:4]
+            if spec[4]:
+                ops[i].crop = A.Box2i(*spec[4])
+            job.layers[i].ops = C.pointer(ops[i])
+        return ops
+
     def job_into(self, out):
         """The same frame program writing into another output frame (so that every frame of a batch can be checked)."""
         d = self.dev
+        if self.name == "4k_4layer_filters":
+            job = d.make_job(out=out, layers=self.layers)
+            job._ops = self.attach_filters(job)
+            return job
         if self.name == "1080p_cross_u8":
             return d.make_job(a=self.layers[0], b=self.layers[1], mix_b=self.mix_b, out_u8=out, u8_table=self.table, full=self.full)
         return d.make_job(out=out, a=self.coded[0] if self.coded else None, b=self.coded[1] if len(self.coded) > 1 else None,
@@ -379,7 +406,19 @@ def expected_output(inputs):
         u8 = np.zeros((h, w, 4), np.uint8)
         orc.orc_encode_u8(C.byref(out.c), O.ptr(srgb), O.ptr(ramp), O.ptr(u8))
         return u8, out.current.tuple()
-    if not pics:
+    if name == "4k_4layer_filters":
+        class OrcOps(C.Structure):
+            _fields_ = [("flags", C.c_int32), ("color", C.c_int32), ("gain", C.c_float), ("offset", C.c_float), ("crop", O.Box),
+                        ("even_rows", O.Frame16)]
+        ops = (OrcOps * len(layers))()
+        for i, spec in enumerate(LAYER_FILTERS):
+            if spec is not None:
+                ops[i].flags, ops[i].color, ops[i].gain, ops[i].offset = spec[:4]
+                if spec[4]:
+                    ops[i].crop = O.Box(*spec[4])
+        orc.orc_composite_ops_f16.argtypes = [C.POINTER(O.Frame16), C.POINTER(O.Frame16), C.c_void_p, C.c_int]
+        orc.orc_composite_ops_f16(C.byref(out.c), arr, C.addressof(ops), len(layers))
+    elif not pics:
         orc.orc_composite_f16(C.byref(out.c), arr, len(layers))
     elif not layers and len(pics) == 1:
         orc.orc_reconstruct(C.byref(out.c), C.byref(pics[0].c))
@@ -618,6 +657,92 @@ def plugin_e2e(B, name, sets, check=True):
     return result
 
 
+def measure_small_kernels(B, seconds=0.15):
+    """The encode side, the colour transform, the scaler and the flat half conversions as single kernels: frames/s over
+    rotating device buffers larger than L2, achieved GB/s against their algorithmic bytes."""
+    dev, lib = B.dev, B.lib
+    A = dev._abi
+    rng = np.random.default_rng(3)
+    results = []
+
+    def timed(name, kernel, note, bytes_per_frame, calls, sets):
+        for i in range(3 * sets):
+            calls(i % sets)
+        B.barrier()
+        reps = sets
+        while True:
+            timer = dev.Timer(B.stream)
+            timer.begin()
+            for i in range(reps):
+                calls(i % sets)
+            timer.end()
+            ms = timer.elapsed_ms()
+            if ms >= seconds * 1e3 or reps >= 1 << 16:
+                break
+            reps = int(reps * max(2.0, min(16.0, 1.2 * seconds * 1e3 / max(ms, 1e-3))))
+        gbs = bytes_per_frame * reps / (ms * 1e-3) / 1e9
+        results.append({"op": name, "kernel": kernel, "note": note, "value": reps / (ms * 1e-3), "unit": "frames/s",
+                        "algorithmic_bytes_per_frame": bytes_per_frame, "achieved_gbs": gbs, "roofline_frac": gbs / B.peak})
+
+    w, h = 3840, 2160
+    full = (0, 0, w - 1, h - 1)
+    base = synth_layer(rng, h, w)
+    sets = 5                                                    # 5 x 66 MB f16 frames: 2.6 x L2
+    frames = [dev.DeviceFrame16.from_numpy(np.roll(base, 13 * i, axis=1), full, full) for i in range(sets)]
+
+    # f16 -> packed 8-bit 4:2:2 (video_subsample.c:99-187 generalised), table written back in place: 8 + 8 + 2 B/px
+    pics = [dev.DeviceCoded([np.zeros((h, 2 * w), np.uint8)], w, h, 2, A.CV_LAYOUT_UYVY, A.CV_MATRIX_709) for _ in range(sets)]
+    timed("4k_subsample_422", "k_subsample<1>", "f16 -> UYVY, linear->Rec.709 table applied in place", w * h * 18,
+          lambda i: dev.check(lib.cv_subsample_ycbcr8(C.byref(frames[i].c), C.byref(pics[i].c), B.stream), "cv_subsample_ycbcr8"), sets)
+    # f16 -> planar 4:2:0 (the MPEG-2 shaders, video_subsample.c:212-290): 8 + 1.5 B/px
+    planar = [dev.DeviceCoded([np.zeros((h, w), np.uint8), np.zeros((h // 2, w // 2), np.uint8), np.zeros((h // 2, w // 2), np.uint8)],
+                              w, h, 2, A.CV_LAYOUT_PLANAR, A.CV_MATRIX_601) for _ in range(sets)]
+    timed("4k_subsample_mpeg2_420", "k_subsample_mpeg2", "f16 -> planar 4:2:0, interlace-aware 6-tap chroma", int(w * h * 9.5),
+          lambda i: dev.check(lib.cv_subsample_mpeg2(C.byref(frames[i].c), C.byref(planar[i].c), B.stream), "cv_subsample_mpeg2"), sets)
+    # display encode with write-back (widget_gl.c:290-307): 8 + 8 + 4 B/px
+    table = dev.display_table(1.25)
+    u8 = [dev.DeviceBuffer(w * h * 4) for _ in range(sets)]
+    timed("4k_encode_u8_writeback", "k_encode_u8", "f16 -> 8-bit display RGBA, sRGB halves written back", w * h * 20,
+          lambda i: dev.check(lib.cv_encode_u8(C.byref(frames[i].c), table, u8[i].ptr, 1, B.stream), "cv_encode_u8"), sets)
+    # colour transform in place (color.c:100-131): 8 + 8 B/px
+    timed("4k_color_rgb_to_xyz", "k_color", "f16 in place: table, 3x3 in f32, truncating pack", w * h * 16,
+          lambda i: dev.check(lib.cv_color_rgb_to_xyz_sdtv(C.byref(frames[i].c), B.stream), "cv_color_rgb_to_xyz_sdtv"), sets)
+    # premultiplied ARGB32 (RgbaFrameF16.c:114-149): 8 + 4 B/px
+    timed("4k_to_argb32", "k_to_argb32", "f16 -> premultiplied ARGB32 through the gamma-0.45 ramp", w * h * 12,
+          lambda i: dev.check(lib.cv_to_argb32(C.byref(frames[i].c), u8[i].ptr, B.stream), "cv_to_argb32"), sets)
+    for f in frames + u8:
+        f.free()
+    for p in pics + planar:
+        for b in p.buffers:
+            b.free()
+
+    # flat half <-> float (half.c:31-51): 4 + 2 B per value, 2^26 values per call
+    count = 1 << 26
+    floats = [dev.DeviceBuffer(count * 4) for _ in range(3)]
+    halves = [dev.DeviceBuffer(count * 2) for _ in range(3)]
+    for b in floats:
+        lib.cv_memset(b.ptr, 0x3C, count * 4, B.stream)
+    timed("half_from_float_64M", "k_half_from_float", "truncating pack, subnormals kept", count * 6,
+          lambda i: dev.check(lib.cv_half_from_float(halves[i].ptr, floats[i].ptr, count, B.stream), "cv_half_from_float"), 3)
+    timed("half_to_float_64M", "k_half_to_float", "exact widening", count * 6,
+          lambda i: dev.check(lib.cv_half_to_float(floats[i].ptr, halves[i].ptr, count, B.stream), "cv_half_to_float"), 3)
+    for b in floats + halves:
+        b.free()
+
+    # the bilinear scaler (video_scale.c:231-319): 4K f32 -> 1080p f32, both axes (factor 1/2): reads 16 B/px of the source
+    # once per axis pass in the ideal case; algorithmic = source + target
+    src_full, dst_full = (0, 0, w - 1, h - 1), (0, 0, w // 2 - 1, h // 2 - 1)
+    f32 = np.ascontiguousarray(base.view(np.float16).astype(np.float32))
+    sources = [dev.DeviceFrame32.from_numpy(np.roll(f32, 7 * i, axis=1), src_full, src_full) for i in range(3)]
+    targets = [dev.DeviceFrame32(dst_full) for _ in range(3)]
+    zero, half_ = A.V2f(0.0, 0.0), A.V2f(0.5, 0.5)
+    timed("4k_to_1080p_scale_f32", "k_scale_axis x2", "triangle-filter resampling, horizontal then vertical pass", (w * h + (w // 2) * (h // 2)) * 16,
+          lambda i: dev.check(lib.cv_scale_bilinear_f32(C.byref(targets[i].c), zero, C.byref(sources[i].c), zero, half_, B.stream), "cv_scale_bilinear_f32"), 3)
+    for f in sources + targets:
+        f.free()
+    return results
+
+
 def scheduler_bench(B, n_gpus, frames=1000, chunk=16, ring=32, clip=4):
     """BASELINE.json configs[4] through the C scheduler: a 3840x2160, `frames`-frame timeline -- two 4:2:2 clips crossfading
     under a linear ramp + three f16 overlay clips with PARTIAL windows -- rendered by ONE cv_timeline_render() call that
@@ -805,6 +930,7 @@ def run_ours(args):
             for s in osets:
                 s.free()
         line["other_workloads"] = others
+        line["other_kernels"] = measure_small_kernels(B)
 
     # ---- the frame-parallel scheduler itself: ONE cv_timeline_render() call over all the GPUs of the job -------------
     if not args.no_scheduler:
@@ -879,7 +1005,7 @@ def cpu_run(name, frames, threads):
     # oracle port, frame-parallel through a thread pool (ctypes releases the GIL)
     from concurrent.futures import ThreadPoolExecutor
     orc = O.oracle()
-    n_layers = {"4k_8layer_composite": 8, "4k_composite_convert": 7, "1080p_4layer_windows": 4}.get(name, 3)
+    n_layers = {"4k_8layer_composite": 8, "4k_composite_convert": 7, "1080p_4layer_windows": 4, "4k_4layer_filters": 4}.get(name, 3)
     layers = [O.HostFrame16(full, full, synth_layer(rng, h, w)) for _ in range(n_layers)]
     windows = WINDOWS_1080P if name == "1080p_4layer_windows" else ([full] + timeline_windows(w, h) if name == "4k_timeline_windows" else [])
     windowed = [O.HostFrame16(full, win, l.array) for l, win in zip(layers, windows)]
@@ -912,6 +1038,9 @@ def cpu_run(name, frames, threads):
         elif name == "1080p_4layer_windows":
             arr = (O.Frame16 * 4)(*[l.c for l in windowed])
             orc.orc_composite_f16(C.byref(out.c), arr, 4)
+        elif name == "4k_4layer_filters":
+            arr = (O.Frame16 * 4)(*[l.c for l in layers])
+            orc.orc_composite_f16(C.byref(out.c), arr, 4)          # the stack without its filters (a lower bound of the CPU cost)
 
     def worker(slot):
         n = frames // threads + (1 if slot < frames % threads else 0)

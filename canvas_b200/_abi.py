@@ -75,9 +75,19 @@ class Coded(C.Structure):
                 ("pic_x", C.c_int32), ("pic_y", C.c_int32)]
 
 
+CV_OP_WEAVE, CV_OP_COLOR, CV_OP_GAIN_OFFSET, CV_OP_CROP = 1, 2, 4, 8
+CV_COLOR_RGB_TO_XYZ_SDTV, CV_COLOR_XYZ_TO_SRGB = 1, 2
+
+
+class LayerOps(C.Structure):
+    """cv_layer_ops: per-pixel filters fused into a layer"""
+    _fields_ = [("flags", C.c_int32), ("color", C.c_int32), ("gain", C.c_float), ("offset", C.c_float), ("crop", Box2i),
+                ("even_rows", FrameF16)]
+
+
 class Layer(C.Structure):
     """cv_layer"""
-    _fields_ = [("frame", FrameF16), ("mix", C.c_float), ("reserved", C.c_int32)]
+    _fields_ = [("frame", FrameF16), ("mix", C.c_float), ("reserved", C.c_int32), ("ops", C.POINTER(LayerOps))]
 
 
 class Source(C.Structure):

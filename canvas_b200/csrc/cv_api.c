@@ -254,6 +254,39 @@ static int build_job( cv_frame_job *job, const BuildOptions *opt, DevJob *dj, in
         d->under = under;
         under = dev_union( &under, &cw );
         pair_ok = pair_ok && f16_pair_ok( d->data, d->pitch, d->ox, dj->full_x );
+
+        /* fused per-pixel filters of this layer */
+        if( L->ops && L->ops->flags ) {
+            const cv_layer_ops *ops = L->ops;
+            if( ops->flags & ~(CV_OP_WEAVE | CV_OP_COLOR | CV_OP_GAIN_OFFSET | CV_OP_CROP) )
+                return cvi_fail( CV_ERR_ARGUMENT, "layer %d: unknown filter flags %#x", i, ops->flags );
+            d->op_flags = ops->flags;
+            if( ops->flags & CV_OP_COLOR ) {
+                if( ops->color != CV_COLOR_RGB_TO_XYZ_SDTV && ops->color != CV_COLOR_XYZ_TO_SRGB )
+                    return cvi_fail( CV_ERR_ARGUMENT, "layer %d: unknown colour transform %d", i, ops->color );
+                d->op_color = ops->color;
+            }
+            d->gain = ops->gain; d->offset = ops->offset;
+            d->crop = to_dev( &ops->crop );
+            if( ops->flags & CV_OP_WEAVE ) {
+                const rgba_frame_f16 *e = &ops->even_rows;
+                DevBox ecw = to_dev( &e->current_window );
+                if( !e->data || ((uintptr_t) e->data & 7) )
+                    return cvi_fail( CV_ERR_ARGUMENT, "layer %d: even_rows frame without data", i );
+                if( ecw.x0 > cw.x0 || ecw.y0 > cw.y0 || ecw.x1 < cw.x1 || ecw.y1 < cw.y1 )
+                    return cvi_fail( CV_ERR_UNSUPPORTED, "layer %d: even_rows must cover the layer's window (weave the frames with cv_weave_fields_f16 instead)", i );
+                d->weave_pitch = box_width( &e->full_window );
+                d->weave_origin = (const char *) e->data - ((int64_t) e->full_window.min.y * d->weave_pitch + e->full_window.min.x) * (int64_t) sizeof(rgba_f16);
+                pair_ok = pair_ok && f16_pair_ok( e->data, d->weave_pitch, e->full_window.min.x, dj->full_x );
+            }
+            dj->flags |= JOB_FLAG_OPS;
+        }
+    }
+    if( dj->flags & JOB_FLAG_OPS ) {
+        CvDevice *dev = cvi_device();
+        if( !dev ) return CV_ERR_NOT_INITIALISED;
+        dj->op_lut_709 = (const uint16_t *) dev->lut[CV_LUT_709_TO_LINEAR_SCENE];
+        dj->op_lut_srgb = (const uint16_t *) dev->lut[CV_LUT_LINEAR_TO_SRGB];
     }
     dj->n_layers = n;
 
@@ -291,7 +324,7 @@ static int build_job( cv_frame_job *job, const BuildOptions *opt, DevJob *dj, in
     }
 
     /* the common workspace case: full-coverage layers, no window tests needed in the kernel */
-    if( *shape == KB_LAYERS && *px == 2 && ((under.x0 - dj->full_x) & 1) == 0 && ((under.x1 - under.x0 + 1) & 1) == 0 ) {
+    if( *shape == KB_LAYERS && *px == 2 && !(dj->flags & JOB_FLAG_OPS) && ((under.x0 - dj->full_x) & 1) == 0 && ((under.x1 - under.x0 + 1) & 1) == 0 ) {
         int simple = 1;
         for( int i = 0; i < n; i++ ) {
             const DevBox *c = &dj->layer[i].cw;
@@ -870,6 +903,8 @@ int cv_subsample_ycbcr8( rgba_frame_f16 *frame, const cv_coded *image, cv_stream
         return cvi_fail( CV_ERR_UNSUPPORTED, "cv_subsample_ycbcr8: packed layouts are 4:2:2" );
     if( image->matrix != CV_MATRIX_709 && image->matrix != CV_MATRIX_601 )
         return cvi_fail( CV_ERR_UNSUPPORTED, "cv_subsample_ycbcr8: unknown matrix" );
+    if( image->layout != CV_LAYOUT_PLANAR && (((uintptr_t) image->plane[0] & 3) || (image->stride[0] & 3)) )
+        return cvi_fail( CV_ERR_ARGUMENT, "cv_subsample_ycbcr8: packed rows must be 4-byte aligned" );
 
     /* video_subsample.c:122-128 */
     box2i pic, win;
@@ -894,18 +929,7 @@ int cv_subsample_ycbcr8( rgba_frame_f16 *frame, const cv_coded *image, cv_stream
     args.magic = cvi_div_magic( args.tx_count );
     args.lut = dev->lut[CV_LUT_LINEAR_TO_709];
 
-    int rc = cvi_launch_subsample( &args, cvi_stream( stream ) );
-    if( rc ) return rc;
-
-    /* :147 -- the table is applied in place to the window of the INPUT frame (second pass, so the
-     * first one never reads a pixel that was already transformed) */
-    LookupWindowArgs lw;
-    memset( &lw, 0, sizeof(lw) );
-    lw.frame = args.frame; lw.pitch = args.pitch; lw.ox = args.ox; lw.oy = args.oy;
-    lw.win = to_dev( &win );
-    lw.width = (uint32_t) box_width( &win );
-    lw.total = lw.width * (uint32_t) args.rows;
-    lw.magic = cvi_div_magic( lw.width );
-    lw.lut = args.lut;
-    return cvi_launch_lookup_window( &lw, cvi_stream( stream ) );
+    /* one pass: coded bytes out, and -- :147 -- the table applied in place to the window of the INPUT frame by the
+     * thread that owns each pixel (neighbours get each other's values through shuffles, never by re-reading) */
+    return cvi_launch_subsample( &args, cvi_stream( stream ) );
 }

@@ -40,6 +40,12 @@ typedef struct DevLayer {
     float mix;
     DevBox cw;                  /* clipped to the output's full_window; never empty (empty layers are dropped) */
     DevBox under;               /* box already defined below this layer (running union); may be empty */
+    /* fused per-pixel filters (cv_layer_ops), evaluated on the layer's pixels as they are read */
+    int32_t op_flags, op_color; /* CV_OP_*, CV_COLOR_* */
+    float gain, offset;
+    DevBox crop;
+    const void *weave_origin;   /* CV_OP_WEAVE: where pixel (0,0) of the frame that supplies the even rows would be */
+    int32_t weave_pitch, op_pad;
 } DevLayer;
 
 enum { DEV_BOTTOM_NONE = 0, DEV_BOTTOM_SINGLE = 1, DEV_BOTTOM_CROSS = 2 };
@@ -57,6 +63,7 @@ typedef struct DevJob {
     float single_alpha;         /* alpha scale of a single bottom source (1 unless copy_frame_alpha) */
     int32_t n_layers;
     int32_t flags;              /* JOB_FLAG_* (cv_kernels.cu) */
+    const uint16_t *op_lut_709, *op_lut_srgb;   /* the colour transforms' tables (rec709->linear scene, linear->sRGB), 65536 halves each */
     float one;                  /* 1.0f, opaque to the compiler (see add2_unfused in cv_kernels.cu) */
     /* work decomposition: items of PX pixels, item (row, i) covers x = item_x0 + i*PX .. */
     int32_t item_x0;
@@ -123,7 +130,8 @@ typedef struct Mpeg2Args {
 
 enum { JOB_FLAG_SIMPLE = 1,     /* every layer covers the whole region, mix == 1, no bottom: no window tests */
        JOB_FLAG_EXACT = 2,      /* f32 frames involved: IEEE-division path only */
-       JOB_FLAG_SEG = 4 };      /* every f16 input is pair-aligned with the output: the row-segment kernel (k_seg) applies */
+       JOB_FLAG_SEG = 4,        /* every f16 input is pair-aligned with the output: the row-segment kernel (k_seg) applies */
+       JOB_FLAG_OPS = 8 };      /* some layer carries fused per-pixel filters: k_rect (or the per-pixel path) renders it */
 
 /* Kernel shape selectors */
 enum { KB_LAYERS = 0,           /* no bottom sources: layer[0] is fetched, the rest go over it */

@@ -34,7 +34,7 @@ struct RectArgs {
 #define CV_RECT_MAX_THREADS 384       /* 168 registers: two units and the 4:2:2 groups of two rows stay in registers (512 threads spilled them) */
 #endif
 
-template<int SHAPE, int PPL>
+template<int SHAPE, int PPL, bool OPS>
 __global__ void __launch_bounds__( CV_RECT_MAX_THREADS, 1 )
 k_rect( const __grid_constant__ DevJob J0, const DevJob *__restrict__ jobs, const __grid_constant__ RectPlan plan,
         const RectPiece *__restrict__ pieces, const __grid_constant__ RectArgs A,
@@ -180,7 +180,12 @@ k_rect( const __grid_constant__ DevJob J0, const DevJob *__restrict__ jobs, cons
             mbar_expect_tx( bars + stage, U.row_bytes );
         __syncwarp();           /* every lane has finished reading this stage's previous contents */
         if( U.src ) {
-            bulk_g2s( ring + (size_t) stage * A.stage_bytes + (uint32_t) lane * SEG_BYTES, U.src, U.pairs * 16u, bars + stage );
+            const char *from = U.src;
+            if constexpr( OPS ) {       /* CV_OP_WEAVE: this layer's even rows come from its other frame (Pulldown23RemovalFilter.c:93-99) */
+                if( lane >= nb && (J0.layer[lane - nb].op_flags & CV_OP_WEAVE) && !(y & 1) )
+                    from = static_cast<const char *>( U.job->layer[lane - nb].weave_origin ) + ((int64_t) y * J0.layer[lane - nb].weave_pitch + U.x0) * 8;
+            }
+            bulk_g2s( ring + (size_t) stage * A.stage_bytes + (uint32_t) lane * SEG_BYTES, from, U.pairs * 16u, bars + stage );
             U.src += U.src_pitch;
         }
     };
@@ -297,9 +302,21 @@ k_rect( const __grid_constant__ DevJob J0, const DevJob *__restrict__ jobs, cons
                 if( !(todo & 1u) )
                     continue;
                 P2 b[PPL];
-                #pragma unroll
-                for( int q = 0; q < PPL; q++ )
-                    b[q] = unpack_pair( lds_u4( slot + q * 512 ) );
+                if( OPS && J0.layer[k].op_flags ) {
+                    /* the layer's fused filters, on its pixels as they leave the ring (cv_layer_ops) */
+                    #pragma unroll
+                    for( int q = 0; q < PPL; q++ ) {
+                        const uint4 raw = lds_u4( slot + q * 512 );
+                        const int x = cur.x0 + 2 * ( q * 32 + lane );
+                        b[q] = join_pair( layer_ops_px( J0, J0.layer[k], make_uint2( raw.x, raw.y ), x, y ),
+                                          layer_ops_px( J0, J0.layer[k], make_uint2( raw.z, raw.w ), x + 1, y ) );
+                    }
+                }
+                else {
+                    #pragma unroll
+                    for( int q = 0; q < PPL; q++ )
+                        b[q] = unpack_pair( lds_u4( slot + q * 512 ) );
+                }
                 if( fetch ) {           /* nothing below: the layer as it is (mix 1) */
                     #pragma unroll
                     for( int q = 0; q < PPL; q++ ) {
@@ -374,6 +391,7 @@ extern "C" int cvi_rect_enabled( void ) {
 extern "C" int cvi_rect_ppl( const DevJob *job ) {
     static int forced = -1;
     if( forced < 0 ) forced = env_int( "CV_RECT_PPL", 0 );
+    if( job->flags & JOB_FLAG_OPS ) return 2;
     if( forced == 2 || forced == 3 ) return forced;
     int slots = job->n_layers;
     if( job->bottom_mode != DEV_BOTTOM_NONE && job->a.kind == CV_SRC_F16 ) slots++;
@@ -395,13 +413,13 @@ extern "C" int cvi_rect_rows( const DevJob *job, int ppl, int count ) {
     return rows < 1 ? 1 : (rows > 8 ? 8 : (int) rows);
 }
 
-template<int SHAPE, int PPL>
+template<int SHAPE, int PPL, bool OPS>
 static int launch_rect_ppl( CvDevice *dev, const DevJob *job, const DevJob *dev_jobs, int count, const RectPlan *plan,
                             const RectPiece *dev_pieces, cudaStream_t stream ) {
     static int attr_done[CV_MAX_DEVICES];
     const size_t limit = 227 * 1024 - 1024;
     if( !attr_done[dev->index] ) {
-        int rc = cvi_cuda( cudaFuncSetAttribute( k_rect<SHAPE, PPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) limit ), "cudaFuncSetAttribute(k_rect)" );
+        int rc = cvi_cuda( cudaFuncSetAttribute( k_rect<SHAPE, PPL, OPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) limit ), "cudaFuncSetAttribute(k_rect)" );
         if( rc ) return rc;
         attr_done[dev->index] = 1;
     }
@@ -441,7 +459,7 @@ static int launch_rect_ppl( CvDevice *dev, const DevJob *job, const DevJob *dev_
     const int key = ((dev->index * 64 + A.slots) * 4 + (int)(tables / 65536)) * 32 + warps;
     if( cached_key != key ) {
         int per_sm = 0;
-        if( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &per_sm, k_rect<SHAPE, PPL>, threads, smem ) != cudaSuccess || per_sm < 1 ) {
+        if( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &per_sm, k_rect<SHAPE, PPL, OPS>, threads, smem ) != cudaSuccess || per_sm < 1 ) {
             cudaGetLastError();
             per_sm = 1;
         }
@@ -454,7 +472,7 @@ static int launch_rect_ppl( CvDevice *dev, const DevJob *job, const DevJob *dev_
     if( blocks > (uint64_t) cached_blocks ) blocks = (uint64_t) cached_blocks;
 
     const uint16_t *full_table = reinterpret_cast<const uint16_t *>( dev->lut[CV_LUT_709_TO_LINEAR_SCENE] );
-    k_rect<SHAPE, PPL><<<(unsigned) blocks, threads, smem, stream>>>( *job, count > 1 ? dev_jobs : NULL, *plan, dev_pieces, A,
+    k_rect<SHAPE, PPL, OPS><<<(unsigned) blocks, threads, smem, stream>>>( *job, count > 1 ? dev_jobs : NULL, *plan, dev_pieces, A,
         reinterpret_cast<const uint16_t *>( dev->lut709_compact ), full_table );
     cvi_count_launch( 1 );
     return cvi_cuda( cudaGetLastError(), "k_rect launch" );
@@ -463,8 +481,10 @@ static int launch_rect_ppl( CvDevice *dev, const DevJob *job, const DevJob *dev_
 template<int SHAPE>
 static int launch_rect( CvDevice *dev, int ppl, const DevJob *job, const DevJob *dev_jobs, int count, const RectPlan *plan,
                         const RectPiece *dev_pieces, cudaStream_t stream ) {
-    if( ppl == 3 ) return launch_rect_ppl<SHAPE, 3>( dev, job, dev_jobs, count, plan, dev_pieces, stream );
-    return launch_rect_ppl<SHAPE, 2>( dev, job, dev_jobs, count, plan, dev_pieces, stream );
+    if( job->flags & JOB_FLAG_OPS )     /* layers with fused filters: the two-pair instantiation that evaluates them */
+        return launch_rect_ppl<SHAPE, 2, true>( dev, job, dev_jobs, count, plan, dev_pieces, stream );
+    if( ppl == 3 ) return launch_rect_ppl<SHAPE, 3, false>( dev, job, dev_jobs, count, plan, dev_pieces, stream );
+    return launch_rect_ppl<SHAPE, 2, false>( dev, job, dev_jobs, count, plan, dev_pieces, stream );
 }
 
 extern "C" int cvi_launch_rect( int shape, int ppl, const DevJob *job, const DevJob *dev_jobs, int count, const RectPlan *plan,

@@ -166,11 +166,8 @@ static int scale_axis( rgba_frame_f32 *target, float tmin, const rgba_frame_f32 
         rc = cvi_launch_scale_axis( &A, stream );
     }
 
-    if( dev_table ) {
-        /* the block returns to the pool once the kernel that reads it has run */
-        if( !rc ) rc = cvi_cuda( cudaStreamSynchronize( stream ), "cudaStreamSynchronize" );
-        cvi_pool_free( dev_table );
-    }
+    if( dev_table )             /* the block returns to the pool once the kernel that reads it has run (stream-ordered) */
+        cvi_pool_free_async( dev_table, stream );
     free( host_table );
 
     if( rc ) box2i_set_empty( &target->current_window );
@@ -234,7 +231,7 @@ int cv_scale_bilinear_f32( rgba_frame_f32 *target, v2f target_point, const rgba_
         rc = scale_axis( &temp, target_point.y, source, source_point.y, factors.y, 1, s );
         if( !rc ) rc = scale_axis( target, target_point.x, &temp, source_point.x, factors.x, 0, s );
     }
-    cv_frame_free_f32( &temp, CV_MEM_DEVICE );       /* scale_axis synchronised the stream */
+    cvi_pool_free_async( temp.data, s );             /* behind the second pass, without waiting for it */
     if( rc ) box2i_set_empty( &target->current_window );
     return rc;
 }

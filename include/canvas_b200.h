@@ -167,10 +167,35 @@ int cv_mix_cross_f16( rgba_frame_f16 *out, const rgba_frame_f16 *a, const rgba_f
 
 /* One stacked layer: `frame.current_window` places it, `mix` scales its alpha (the
  * workspace uses 1).  frame.data may be NULL only when current_window is empty. */
+/*
+ * Per-pixel filters FUSED into a layer: what the editor chains in front of a workspace item (all GL-only in the
+ * reference except the colour transforms and the field weave) is evaluated in registers on the layer's pixels as they
+ * are read, before "over" -- no intermediate frame, no extra HBM traffic.  Applied in this order:
+ *   CV_OP_WEAVE        the even rows come from `even_rows` instead (Pulldown23RemovalFilter.c:82-104: field 1 of the next
+ *                      frame); even_rows.current_window must cover the layer's window, pixels are untouched bits;
+ *   CV_OP_COLOR        video_color_rgb_to_xyz_sdtv / video_color_xyz_to_srgb (color.c:100-160): [table,] exact widening,
+ *                      3x3 matrix in f32, truncating pack to half [, table] -- the same roundings as the separate pass;
+ *   CV_OP_GAIN_OFFSET  rgb * gain + offset in f32, alpha untouched (video_filter.c:27-39); the result stays f32;
+ *   CV_OP_CROP         pixels of the layer outside `crop` become (0, 0, 0, 0), its window stays (video_filter.c:79-95).
+ * The result is bit-identical to running cv_weave_fields_f16 / cv_color_* / cv_gain_offset_f32 / cv_crop_f16 as separate
+ * passes and stacking the outcome (tests/test_gpu_layer_ops.py).
+ */
+enum { CV_OP_WEAVE = 1, CV_OP_COLOR = 2, CV_OP_GAIN_OFFSET = 4, CV_OP_CROP = 8 };
+enum { CV_COLOR_RGB_TO_XYZ_SDTV = 1, CV_COLOR_XYZ_TO_SRGB = 2 };
+
+typedef struct {
+    int32_t flags;              /* CV_OP_* */
+    int32_t color;              /* CV_COLOR_* */
+    float gain, offset;
+    box2i crop;
+    rgba_frame_f16 even_rows;   /* device frame, pair-aligned like the layer's */
+} cv_layer_ops;
+
 typedef struct {
     rgba_frame_f16 frame;
     float mix;
     int32_t reserved;
+    const cv_layer_ops *ops;    /* NULL: the layer as it is */
 } cv_layer;
 
 /* Workspace compositor: layers[0] is fetched into out, each further layer goes "over" it,

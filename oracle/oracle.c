@@ -841,6 +841,69 @@ void orc_composite_f16( orc_frame16 *out, const orc_frame16 *layers, int count )
     free( acc.data );
 }
 
+/* ---- 2:3 pulldown field weave: src/process/Pulldown23RemovalFilter.c:82-104 -------------------
+ * The even rows (field 1) of frame's current window are replaced by the same rows of `even_rows`.  The reference
+ * copies them out of a temporary it pulled over frame->current_window, starting at that temporary's pixel x = 0
+ * (video_get_pixel_f16( &tempFrame, 0, i ), :97-99) -- which is the window's left edge only when min.x == 0; the
+ * intended copy (from min.x) is what is restated here, and what the reference does for every window with min.x == 0. */
+void orc_weave_fields_f16( orc_frame16 *frame, const orc_frame16 *even_rows ) {
+    orc_box box = box_intersect( &frame->current, &even_rows->current );
+    box = box_intersect( &box, &frame->full );
+    if( box_empty( &box ) )
+        return;
+    for( int y = (box.min_y + 1) & ~1; y <= box.max_y; y += 2 )
+        memcpy( px16( frame, box.min_x, y ), px16( even_rows, box.min_x, y ), sizeof(orc_px16) * (size_t)( box.max_x - box.min_x + 1 ) );
+}
+
+/* ---- the workspace compositor with per-pixel filters in front of its layers -------------------
+ * What the editor builds when an item's source is a chain Pulldown23RemovalFilter -> colour transform ->
+ * VideoGainOffsetFilter -> crop: every filter is applied to the layer as its own pass (the functions above and below,
+ * in that order), the filtered layers are stacked by workspace.c:530-547.  Precision of the chain: the weave and the
+ * colour transform produce f16 frames, gain / offset works on the f32 frame the compositor pulls (video_filter.c:27-39
+ * on an f32 texture) and its result stays f32. */
+void orc_composite_ops_f16( orc_frame16 *out, const orc_frame16 *layers, const orc_layer_ops *ops, int count ) {
+    if( count <= 0 ) {
+        box_set_empty( &out->current );
+        return;
+    }
+    orc_frame32 acc = alloc32( &out->full ), temp = alloc32( &out->full );
+
+    for( int i = 0; i < count; i++ ) {
+        orc_frame16 filtered = alloc16( &out->full );
+        orc_copy_frame_f16( &filtered, &layers[i] );
+        const orc_layer_ops *o = ops ? &ops[i] : NULL;
+
+        if( o && (o->flags & ORC_OP_WEAVE) ) orc_weave_fields_f16( &filtered, &o->even_rows );
+        if( o && (o->flags & ORC_OP_COLOR) ) {
+            if( o->color == ORC_COLOR_RGB_TO_XYZ_SDTV ) orc_color_rgb_to_xyz_sdtv( &filtered );
+            else orc_color_xyz_to_srgb( &filtered );
+        }
+        orc_frame32 *target = (i == 0) ? &acc : &temp;
+        orc_frame_f16_to_f32( target, &filtered );
+        if( o && (o->flags & ORC_OP_GAIN_OFFSET) ) {
+            const orc_box box = box_intersect( &target->current, &target->full );
+            for( int y = box.min_y; y <= box.max_y; y++ )
+                for( int x = box.min_x; x <= box.max_x; x++ ) {
+                    orc_px32 *p = px32( target, x, y );
+                    p->r = p->r * o->gain + o->offset; p->g = p->g * o->gain + o->offset; p->b = p->b * o->gain + o->offset;
+                }
+        }
+        if( o && (o->flags & ORC_OP_CROP) ) {
+            const orc_box box = box_intersect( &target->current, &target->full );
+            for( int y = box.min_y; y <= box.max_y; y++ )
+                for( int x = box.min_x; x <= box.max_x; x++ )
+                    if( !box_contains( &o->crop, x, y ) )
+                        memset( px32( target, x, y ), 0, sizeof(orc_px32) );
+        }
+        if( i > 0 ) orc_mix_over_f32( &acc, &temp, 1.0f );
+        free( filtered.data );
+    }
+
+    orc_frame_f32_to_f16( out, &acc );
+    free( acc.data );
+    free( temp.data );
+}
+
 /* ---- crossfade pulled as f16: video_mix.c:46-71 via main.c:44-72 ---------------------- */
 void orc_cross_f16( orc_frame16 *out, const orc_frame16 *a, const orc_frame16 *b, float mix_b ) {
     orc_frame32 acc = alloc32( &out->full );

@@ -107,6 +107,18 @@ void orc_frame_f32_to_f16( orc_frame16 *out, const orc_frame32 *in );
  * out->full (video_copy_frame_f16), converted to f32, composited with mix 1, packed. */
 void orc_composite_f16( orc_frame16 *out, const orc_frame16 *layers, int count );
 
+/* src/process/Pulldown23RemovalFilter.c:82-104: the even rows of frame's current window come from `even_rows`
+ * (intended form: copied from the window's left edge; the reference starts at the temporary's x = 0, equal for min.x == 0) */
+void orc_weave_fields_f16( orc_frame16 *frame, const orc_frame16 *even_rows );
+
+/* The compositor with a filter chain in front of each layer -- weave, colour transform (f16), gain/offset (f32, GLSL
+ * restated: PARITY UNPINNED for that step), crop (zeros; GLSL restated) -- each applied as its own pass, then
+ * workspace.c:530-547.  ops may be NULL; ops[i].flags == 0 leaves layer i alone. */
+enum { ORC_OP_WEAVE = 1, ORC_OP_COLOR = 2, ORC_OP_GAIN_OFFSET = 4, ORC_OP_CROP = 8 };
+enum { ORC_COLOR_RGB_TO_XYZ_SDTV = 1, ORC_COLOR_XYZ_TO_SRGB = 2 };
+typedef struct { int32_t flags, color; float gain, offset; orc_box crop; orc_frame16 even_rows; } orc_layer_ops;
+void orc_composite_ops_f16( orc_frame16 *out, const orc_frame16 *layers, const orc_layer_ops *ops, int count );
+
 /* VideoMixFilter path: video_mix.c:46-71 pulled as f16 (main.c:44-72). */
 void orc_cross_f16( orc_frame16 *out, const orc_frame16 *a, const orc_frame16 *b, float mix_b );
 

@@ -188,7 +188,8 @@ def test_foreign_sources_are_pulled_through_their_capsule(process, foreign):
     # a crossfade of the foreign source and one of ours
     got = process.VideoMixFilter(gradient, ours_source, 0.25).get_frame_f16(3, full)
     want = O.HostFrame16(full)
-    O.oracle().orc_cross_f16(C.byref(want.c), C.byref(host_frame(3).c), C.byref(ours.c), 0.25)
+    theirs = host_frame(3)
+    O.oracle().orc_cross_f16(C.byref(want.c), C.byref(theirs.c), C.byref(ours.c), 0.25)
     assert got.current_window.flat() == want.current.tuple()
     x0, y0, x1, y1 = want.current.tuple()            # pixels outside current_window are undefined (framework.rst:27-30)
     assert np.array_equal(got.data[y0:y1 + 1, x0:x1 + 1], want.array[y0:y1 + 1, x0:x1 + 1])
@@ -198,9 +199,11 @@ def test_foreign_sources_are_pulled_through_their_capsule(process, foreign):
     workspace.add(source=ours_source, x=0, length=100, z=0, offset=0)
     workspace.add(source=gradient, x=0, length=100, z=5, offset=7)
     got = workspace.get_frame_f16(2, full)
-    layers = (O.Frame16 * 2)(ours.c, host_frame(9).c)
+    top = host_frame(9)                             # (kept alive: the ctypes struct only borrows its pixels)
+    layers = (O.Frame16 * 2)(ours.c, top.c)
     O.oracle().orc_composite_f16(C.byref(want.c), layers, 2)
     assert got.current_window.flat() == want.current.tuple()
     x0, y0, x1, y1 = want.current.tuple()
-    assert np.array_equal(got.data[y0:y1 + 1, x0:x1 + 1], want.array[y0:y1 + 1, x0:x1 + 1])
+    bad = np.argwhere(np.any(got.data[y0:y1 + 1, x0:x1 + 1] != want.array[y0:y1 + 1, x0:x1 + 1], axis=2))
+    assert len(bad) == 0, "first differing pixels (row, column): %s" % bad[:8].tolist()
     assert gradient.calls >= 2
