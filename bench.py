@@ -503,6 +503,16 @@ class Bench:
         self.peak, self.peak_source = load_peaks()
         self.traffic = load_traffic()
 
+    def host_signal(self, key):
+        if self.dist is not None:
+            self.dist.distributed_c10d._get_default_store().set(key, "1")
+
+    def host_wait(self, key):
+        """blocks on the rendezvous (TCP) store: no GPU work while waiting"""
+        if self.dist is not None:
+            import datetime
+            self.dist.distributed_c10d._get_default_store().wait([key], datetime.timedelta(seconds=600))
+
     def barrier(self):
         self.dev.check(self.lib.cv_device_sync(), "cv_device_sync")
         if self.dist is not None:
@@ -842,14 +852,15 @@ def scheduler_bench(B, n_gpus, frames=1000, chunk=16, ring=32, clip=4):
 
     coverage = sum((b[2] - b[0] + 1) * (b[3] - b[1] + 1) for b in windows)
     result = {"n_gpus": n_gpus, "frames": frames, "chunk": chunk, "ring": ring, "workload": "4k_timeline_windows (BASELINE.json configs[4])"}
-    for mode in ("resident", "pulled_u8"):
-        items = make_items(mode == "pulled_u8")
+    modes = ("resident", "pulled_u8") if not os.environ.get("CV_BENCH_SCHEDULER_MODES") else tuple(os.environ["CV_BENCH_SCHEDULER_MODES"].split(","))
+    for mode in modes:                      # also: "pulled" (4:2:2 in, f16 left in HBM), "resident_u8" (8-bit out only)
+        items = make_items(mode.startswith("pulled"))
         run = A.TimelineRun()
         run.items, run.item_count, run.n_gpus = items, 4, n_gpus
         run.first, run.last, run.chunk, run.targets = 0, frames - 1, chunk, targets
-        for g in range(n_gpus):             # the 8-bit targets exist only in the end-to-end mode
-            targets[g].out_u8 = C.cast(u8_rings[g], C.POINTER(C.c_void_p)) if mode == "pulled_u8" else None
-        if mode == "pulled_u8":
+        for g in range(n_gpus):             # the 8-bit targets exist only in the end-to-end modes
+            targets[g].out_u8 = C.cast(u8_rings[g], C.POINTER(C.c_void_p)) if mode.endswith("_u8") else None
+        if mode.endswith("_u8"):
             run.sink = sink
         stats = (A.TimelineStats * n_gpus)()
         warm = A.TimelineRun()
@@ -861,11 +872,11 @@ def scheduler_bench(B, n_gpus, frames=1000, chunk=16, ring=32, clip=4):
         dev.check(lib.cv_timeline_render(C.byref(run), stats), "cv_timeline_render")
         wall = time.perf_counter() - t0
         device_ms = max(s.device_ms for s in stats)
-        bytes_per_frame = 4 * w * h + 8 * coverage + 8 * w * h + (4 * w * h if mode == "pulled_u8" else 0)
+        bytes_per_frame = 4 * w * h + 8 * coverage + 8 * w * h + (4 * w * h if mode.endswith("_u8") else 0)
         result[mode] = {"value": frames / wall, "unit": "frames/s", "wall_ms": wall * 1e3, "slowest_gpu_device_ms": device_ms,
                         "device_fps": frames / (device_ms * 1e-3), "gpu_launches": int(lib.cv_kernel_launches() - before),
                         "frames_per_gpu": [int(s.frames) for s in stats], "algorithmic_gb_per_s": bytes_per_frame * frames / wall / 1e9,
-                        "h2d_bytes_per_frame": (sum(int(s.h2d_bytes) for s in stats) / frames), "d2h_bytes_per_frame": (4 * w * h if mode == "pulled_u8" else 0)}
+                        "h2d_bytes_per_frame": (sum(int(s.h2d_bytes) for s in stats) / frames), "d2h_bytes_per_frame": (4 * w * h if mode.endswith("_u8") else 0)}
     for k in keep:
         if hasattr(k, "free"):
             try:
@@ -934,11 +945,18 @@ def run_ours(args):
 
     # ---- the frame-parallel scheduler itself: ONE cv_timeline_render() call over all the GPUs of the job -------------
     if not args.no_scheduler:
-        B.barrier()                         # the other ranks idle from here on (their GPUs are driven by rank 0's workers)
+        B.barrier()
+        # The other ranks' GPUs are driven by rank 0's worker threads now.  They must idle on the HOST: an NCCL barrier
+        # would park a spinning kernel on every waiting GPU, so they wait on a key of the rendezvous store instead.
         if B.rank == 0:
             n_sched = max(B.world, args.gpus if B.dist is None else B.world)
             n_sched = min(n_sched, B.lib.cv_device_count())
-            line["scheduler"] = scheduler_bench(B, n_sched, frames=1000)
+            try:
+                line["scheduler"] = scheduler_bench(B, n_sched, frames=1000)
+            finally:
+                B.host_signal("scheduler_done")
+        else:
+            B.host_wait("scheduler_done")
         B.barrier()
 
     if B.rank == 0 and B.world == 1 and not args.no_cpu_baseline:

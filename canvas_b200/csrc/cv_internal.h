@@ -204,6 +204,10 @@ void cvi_count_launch( unsigned n );
 int cvi_pool_alloc( void **ptr, size_t bytes );
 int cvi_pool_free( void *ptr );
 int cvi_pool_free_async( void *ptr, cudaStream_t stream );
+/* pooled pinned host memory for staging (never returned to the OS before cv_shutdown) */
+int cvi_pinned_alloc( void **ptr, size_t bytes );
+void cvi_pinned_free( void *ptr );
+void cvi_pinned_release_all( void );
 
 /* per-thread context of the framework.h entry points (cv_host_ctx.c): own stream, pinned staging slabs */
 enum { CV_HOST_SLABS = 4 };

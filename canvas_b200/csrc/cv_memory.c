@@ -162,6 +162,65 @@ void cvi_pool_release_all( int device ) {
     memset( pool, 0, sizeof(*pool) );
 }
 
+/* ------------------------------------------------------------ pooled pinned staging memory */
+
+/* cudaMallocHost costs milliseconds per call: the staging buffers of the timeline workers are kept in a process-wide
+ * pool (same size classes as the device pool) and handed out again by the next cv_timeline_render() call. */
+typedef struct PinnedBlock { void *ptr; size_t bytes; int in_use; } PinnedBlock;
+static PinnedBlock *g_pinned;
+static int g_pinned_count, g_pinned_capacity;
+static pthread_mutex_t g_pinned_lock = PTHREAD_MUTEX_INITIALIZER;
+
+int cvi_pinned_alloc( void **ptr, size_t bytes ) {
+    if( bytes == 0 ) bytes = 1;
+    bytes = (bytes + POOL_GRANULE - 1) & ~(POOL_GRANULE - 1);
+    pthread_mutex_lock( &g_pinned_lock );
+    int best = -1;
+    for( int i = 0; i < g_pinned_count; i++ )
+        if( !g_pinned[i].in_use && g_pinned[i].bytes >= bytes && g_pinned[i].bytes <= bytes + bytes / 4 &&
+                (best < 0 || g_pinned[i].bytes < g_pinned[best].bytes) )
+            best = i;
+    if( best >= 0 ) {
+        g_pinned[best].in_use = 1;
+        *ptr = g_pinned[best].ptr;
+        pthread_mutex_unlock( &g_pinned_lock );
+        return CV_OK;
+    }
+    pthread_mutex_unlock( &g_pinned_lock );
+
+    void *fresh = NULL;
+    int rc = cvi_cuda( cudaMallocHost( &fresh, bytes ), "cudaMallocHost(staging)" );
+    if( rc ) return rc;
+    pthread_mutex_lock( &g_pinned_lock );
+    if( g_pinned_count == g_pinned_capacity ) {
+        g_pinned_capacity = g_pinned_capacity ? g_pinned_capacity * 2 : 64;
+        g_pinned = (PinnedBlock *) realloc( g_pinned, sizeof(PinnedBlock) * (size_t) g_pinned_capacity );
+    }
+    g_pinned[g_pinned_count].ptr = fresh; g_pinned[g_pinned_count].bytes = bytes; g_pinned[g_pinned_count].in_use = 1;
+    g_pinned_count++;
+    pthread_mutex_unlock( &g_pinned_lock );
+    *ptr = fresh;
+    return CV_OK;
+}
+
+void cvi_pinned_free( void *ptr ) {
+    if( !ptr ) return;
+    pthread_mutex_lock( &g_pinned_lock );
+    for( int i = 0; i < g_pinned_count; i++ )
+        if( g_pinned[i].ptr == ptr ) { g_pinned[i].in_use = 0; break; }
+    pthread_mutex_unlock( &g_pinned_lock );
+}
+
+void cvi_pinned_release_all( void ) {
+    pthread_mutex_lock( &g_pinned_lock );
+    for( int i = 0; i < g_pinned_count; i++ )
+        cudaFreeHost( g_pinned[i].ptr );
+    free( g_pinned );
+    g_pinned = NULL;
+    g_pinned_count = g_pinned_capacity = 0;
+    pthread_mutex_unlock( &g_pinned_lock );
+}
+
 /* ------------------------------------------------------------ raw memory */
 
 int cv_malloc( void **ptr, size_t bytes, int where ) {

@@ -263,6 +263,7 @@ void cv_shutdown( void ) {
         cudaStreamDestroy( dev->stream );
         dev->ready = 0;
     }
+    cvi_pinned_release_all();
     t_device = -1;
     pthread_mutex_unlock( &g_init_lock );
 }

@@ -220,14 +220,19 @@ static void bind_to_device_node( int device ) {
 typedef struct Stage { void *pinned, *dev; size_t bytes; coded_image *held; } Stage;
 typedef struct Entry { Stage stage[CV_PULLS_MAX]; } Entry;
 
-static int stage_reserve( Stage *s, size_t bytes ) {
-    if( s->bytes >= bytes ) return CV_OK;
-    if( s->pinned ) cv_free( s->pinned, CV_MEM_PINNED );
-    if( s->dev ) cv_free( s->dev, CV_MEM_DEVICE );
-    s->pinned = s->dev = NULL; s->bytes = 0;
-    int rc = cv_malloc( &s->pinned, bytes, CV_MEM_PINNED );
-    if( !rc ) rc = cv_malloc( &s->dev, bytes, CV_MEM_DEVICE );
-    if( !rc ) s->bytes = bytes;
+/* device buffer (and, when the picture has to be staged, pinned host buffer) of at least `bytes`; both come from pools,
+ * so a second cv_timeline_render() call finds the blocks of the first */
+static int stage_reserve( Stage *s, size_t bytes, int need_pinned ) {
+    int rc = CV_OK;
+    if( s->bytes < bytes ) {
+        if( s->pinned ) cvi_pinned_free( s->pinned );
+        if( s->dev ) cv_free( s->dev, CV_MEM_DEVICE );
+        s->pinned = s->dev = NULL; s->bytes = 0;
+        rc = cv_malloc( &s->dev, bytes, CV_MEM_DEVICE );
+        if( !rc ) s->bytes = bytes;
+    }
+    if( !rc && need_pinned && !s->pinned )
+        rc = cvi_pinned_alloc( &s->pinned, s->bytes );
     return rc;
 }
 
@@ -258,8 +263,8 @@ static int pull_coded( const cv_pull *pull, int64_t source_frame, Stage *st, cv_
         size[i] = ((size_t) image->stride[i] * (size_t) lines + 255) & ~(size_t) 255;
         total += size[i];
     }
-    int rc = stage_reserve( st, total ? total : 256 );
-    const int direct = !rc && total && host_memory_is_pinned( image->data[0] );
+    const int direct = total && host_memory_is_pinned( image->data[0] );        /* pinned already: copied from where it lies */
+    int rc = stage_reserve( st, total ? total : 256, !direct );
 
     *out = pull->format;
     size_t at = 0;
@@ -288,7 +293,7 @@ static int pull_video( const cv_pull *pull, int64_t source_frame, Stage *st, cv_
     v2i size;
     box2i_get_size( &pull->full_window, &size );
     const size_t pitch = (size_t) size.x * sizeof(rgba_f16), bytes = pitch * (size_t) size.y;
-    int rc = stage_reserve( st, bytes ? bytes : 256 );
+    int rc = stage_reserve( st, bytes ? bytes : 256, 1 );
     if( rc ) return rc;
 
     rgba_frame_f16 host;
@@ -467,7 +472,7 @@ fail:
             for( int j = 0; j < CV_PULLS_MAX; j++ ) {
                 Stage *st = &entries[i].stage[j];
                 stage_release_held( st );
-                if( st->pinned ) cv_free( st->pinned, CV_MEM_PINNED );
+                if( st->pinned ) cvi_pinned_free( st->pinned );
                 if( st->dev ) cv_free( st->dev, CV_MEM_DEVICE );
             }
         free( entries );
