@@ -1,22 +1,61 @@
-"""Prints the handful of ncu metrics the profiles/ notes quote from a .ncu-rep (run here, no GPU needed)."""
-import csv, subprocess, sys
-rep = sys.argv[1]
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-rows = list(csv.reader(raw.splitlines()))
-hdr, units = rows[0], rows[1]
-keys = ["Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
-        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "launch__grid_size", "launch__block_size",
-        "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic", "sm__warps_active.avg.pct_of_peak_sustained_active",
-        "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
-        "l1tex__data_pipe_lsu_wavefronts.sum.pct_of_peak_sustained_elapsed", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
-        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "sm__inst_executed_pipe_fmaheavy.avg.pct_of_peak_sustained_active",
-        "sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
-        "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
-        "lts__t_sector_hit_rate.pct", "local_load", "smsp__inst_executed_op_local"]
-for r in rows[2:]:
-    for h, u, v in zip(hdr, units, r):
-        if any(h == k or (k in h and "local" in k) for k in keys):
-            print("%-75s %-12s %s" % (h, u, v))
-    for h, u, v in zip(hdr, units, r):
-        if "stalled" in h and "per_issue_active" in h and float(v or 0) > 0.15:
-            print("%-75s %s" % (h.replace("smsp__average_warps_issue_stalled_", "stall "), v))
+#!/usr/bin/env python
+"""scripts/ncu_summary.py -- turns the `ncu --set full` captures of scripts/gpu_profile_r2.sh (their raw pages, gpurun_out/p2_<workload>_raw.csv)
+into what the repository keeps: profiles/traffic.json (dram__bytes_read.sum + dram__bytes_write.sum per FRAME and per launch, by
+workload -- bench.py's roofline.traffic reads it), profiles/r2_<workload>_raw.csv (the raw metric page) and a one-line digest
+per workload on stdout for profiles/r2_kernels.md."""
+import csv
+import glob
+import json
+import os
+import re
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench
+
+
+def unit_scale(unit):
+    return {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}.get(unit, 1.0)
+
+
+def main():
+    traffic = {}
+    for exported in sorted(glob.glob(os.path.join(ROOT, "gpurun_out", "p2_*_raw.csv"))):
+        workload = os.path.basename(exported)[3:-8]
+        if workload not in bench.WORKLOADS:
+            continue
+        raw = open(exported).read()
+        if not raw.strip():
+            continue
+        with open(os.path.join(ROOT, "profiles", "r2_%s_raw.csv" % workload), "w") as f:
+            f.write(raw)
+        digest = os.path.join(ROOT, "gpurun_out", "p2_%s_digest.txt" % workload)
+        if os.path.exists(digest):
+            with open(os.path.join(ROOT, "profiles", "r2_%s_digest.txt" % workload), "w") as f:
+                f.write(open(digest).read())
+        rows = list(csv.reader(raw.splitlines()))
+        m = {h: (v, u) for h, u, v in zip(rows[0], rows[1], rows[-1])}
+        num = lambda k: float(m[k][0].replace(",", "")) * unit_scale(m[k][1])
+        dram = num("dram__bytes_read.sum") + num("dram__bytes_write.sum")
+        ms = float(m["gpu__time_duration.sum"][0].replace(",", "")) * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}[m["gpu__time_duration.sum"][1]]
+        kernel = re.sub(r"\(.*", "", m["Kernel Name"][0])
+        algorithmic = bench.workload_bytes(workload)
+        frames = max(1, round(dram / algorithmic))              # a batch launch renders many frames: traffic ~ algorithmic bytes
+        traffic[workload] = {"dram_bytes_per_frame": dram / frames, "dram_bytes_per_launch": dram, "frames_per_launch": frames,
+                             "algorithmic_bytes_per_frame": algorithmic, "kernel": kernel, "launch_ms": ms,
+                             "registers_per_thread": int(float(m["launch__registers_per_thread"][0])),
+                             "warps_active_per_sm": float(m["sm__warps_active.avg.per_cycle_active"][0]),
+                             "issue_active_pct": float(m["smsp__issue_active.avg.pct_of_peak_sustained_active"][0]),
+                             "source": "profiles/r2_%s_raw.csv (ncu --set full, scripts/gpu_profile_r2.sh)" % workload}
+        print("%-22s %-28s %8.3f ms  dram %.1f MB/frame vs algorithmic %.1f MB (x%.3f)  regs %d  warps/SM %.1f  issue %.0f%%" % (
+            workload, kernel[:28], ms, dram / frames / 1e6, algorithmic / 1e6, dram / frames / algorithmic,
+            traffic[workload]["registers_per_thread"], traffic[workload]["warps_active_per_sm"], traffic[workload]["issue_active_pct"]))
+    if traffic:
+        with open(os.path.join(ROOT, "profiles", "traffic.json"), "w") as f:
+            json.dump(traffic, f, indent=1, sort_keys=True)
+
+
+if __name__ == "__main__":
+    main()
