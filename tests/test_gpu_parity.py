@@ -152,6 +152,37 @@ def test_cross_matches_oracle(dev, mix, windows):
     assert_frames_equal(out.download(), out.current.tuple(), want, "cross mix=%r windows=%r" % (mix, windows))
 
 
+TINY_MIXES = [1e-20, 1e-38, 1.1754944e-38, 1e-42, 5.0e-8, 1.0 - 5.96e-8]      # ... FLT_MIN, a subnormal, just under 2^-24, 1 - 2^-24
+
+
+@pytest.mark.parametrize("mix", TINY_MIXES)
+def test_tiny_mixes_keep_the_ieee_division(dev, mix):
+    """A positive mix below 2^-24 makes alpha * mix smaller than anything the shared-reciprocal division of the fast path
+    is exact for: such jobs must take the IEEE-division path.  The crossfade (video_mix.c:192-206) with the
+    weight on either side, and a layer whose alpha is scaled by it (video_mix.c:323-337)."""
+    full = (0, 0, 63, 35)
+    a, b = O.synth_frame(full, 21, full), O.synth_frame(full, 22, (8, 2, 60, 30))
+    for m in (mix, 1.0 - mix if mix < 0.5 else mix):
+        want = O.HostFrame16(full)
+        O.oracle().orc_cross_f16(C.byref(want.c), C.byref(a.c), C.byref(b.c), m)
+        out = poisoned(dev, full)
+        dev.mix_cross(out, to_device(dev, a), to_device(dev, b), m)
+        assert_frames_equal(out.download(), out.current.tuple(), want, "cross mix=%r" % m)
+
+    # a layer over a bottom with its alpha scaled by the tiny mix: the f32 frame operations are the oracle here
+    bottom32, top32, acc = O.HostFrame32(full), O.HostFrame32(full), O.HostFrame32(full)
+    O.oracle().orc_frame_f16_to_f32(C.byref(bottom32.c), C.byref(a.c))
+    O.oracle().orc_frame_f16_to_f32(C.byref(top32.c), C.byref(b.c))
+    O.oracle().orc_copy_frame_alpha_f32(C.byref(acc.c), C.byref(bottom32.c), 1.0)
+    O.oracle().orc_mix_over_f32(C.byref(acc.c), C.byref(top32.c), mix)
+    want = O.HostFrame16(full)
+    O.oracle().orc_frame_f32_to_f16(C.byref(want.c), C.byref(acc.c))
+    out = poisoned(dev, full)
+    dev.composite_over(out, [to_device(dev, a), (to_device(dev, b), mix)])
+    dev.sync()
+    assert_frames_equal(out.download(), out.current.tuple(), want, "layer mix=%r" % mix)
+
+
 # ------------------------------------------------------------------ conversion
 
 def device_coded(dev, pic, zero=False):
