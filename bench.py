@@ -760,7 +760,9 @@ def scheduler_bench(B, n_gpus, frames=1000, chunk=16, ring=32, clip=4):
       resident   every clip resident on every GPU, f16 output left in HBM (the device-side capability of the scheduler);
       pulled_u8  end to end: the 4:2:2 pictures are PULLED from pinned host memory through coded_image_source.getFrame
                  (4 B/px host->device per frame), overlays resident (static graphics), the 8-bit display encode of every
-                 frame copied to pinned host memory from the sink (4 B/px device->host)."""
+                 frame copied to pinned host memory from the sink (4 B/px device->host);
+      pulled_422 the same input, the result subsampled to 8-bit 4:2:2 on the device (cv_subsample_ycbcr8 from the sink)
+                 and copied back: 2 B/px device->host, what an encoder takes."""
     from canvas_b200 import _abi as A
     dev, lib = B.dev, B.lib
     w, h = 3840, 2160
@@ -850,9 +852,25 @@ def scheduler_bench(B, n_gpus, frames=1000, chunk=16, ring=32, clip=4):
         counters[slot] += 1
         return lib.cv_download(C.c_void_p(pinned_out[slot].ptr.value + k * w * h * 4), job.contents.out_u8, w * h * 4, stream)
 
+    # 4:2:2 8-bit out (what an encoder takes, X264VideoEncoder.c:295-312): cv_subsample_ycbcr8 from the sink, 2 B/px back
+    coded_out = []
+    for g in range(n_gpus):
+        dev.init(g)
+        coded_out.append([dev.DeviceCoded([np.zeros((h, 2 * w), np.uint8)], w, h, 2, A.CV_LAYOUT_UYVY, A.CV_MATRIX_709) for _ in range(ring)])
+    dev.init(B.local)
+    keep.append(coded_out)
+
+    @A.TIMELINE_SINK
+    def sink_422(user, slot, frame, job, stream):
+        k = counters[slot] % ring
+        counters[slot] += 1
+        pic = coded_out[slot][k]
+        rc = lib.cv_subsample_ycbcr8(job.contents.out, C.byref(pic.c), stream)
+        return rc or lib.cv_download(C.c_void_p(pinned_out[slot].ptr.value + k * w * h * 4), pic.buffers[0].ptr, w * h * 2, stream)
+
     coverage = sum((b[2] - b[0] + 1) * (b[3] - b[1] + 1) for b in windows)
     result = {"n_gpus": n_gpus, "frames": frames, "chunk": chunk, "ring": ring, "workload": "4k_timeline_windows (BASELINE.json configs[4])"}
-    modes = ("resident", "pulled_u8") if not os.environ.get("CV_BENCH_SCHEDULER_MODES") else tuple(os.environ["CV_BENCH_SCHEDULER_MODES"].split(","))
+    modes = ("resident", "pulled_u8", "pulled_422") if not os.environ.get("CV_BENCH_SCHEDULER_MODES") else tuple(os.environ["CV_BENCH_SCHEDULER_MODES"].split(","))
     for mode in modes:                      # also: "pulled" (4:2:2 in, f16 left in HBM), "resident_u8" (8-bit out only)
         items = make_items(mode.startswith("pulled"))
         run = A.TimelineRun()
@@ -862,6 +880,8 @@ def scheduler_bench(B, n_gpus, frames=1000, chunk=16, ring=32, clip=4):
             targets[g].out_u8 = C.cast(u8_rings[g], C.POINTER(C.c_void_p)) if mode.endswith("_u8") else None
         if mode.endswith("_u8"):
             run.sink = sink
+        elif mode.endswith("_422"):
+            run.sink = sink_422
         stats = (A.TimelineStats * n_gpus)()
         warm = A.TimelineRun()
         C.memmove(C.byref(warm), C.byref(run), C.sizeof(run))
@@ -872,11 +892,11 @@ def scheduler_bench(B, n_gpus, frames=1000, chunk=16, ring=32, clip=4):
         dev.check(lib.cv_timeline_render(C.byref(run), stats), "cv_timeline_render")
         wall = time.perf_counter() - t0
         device_ms = max(s.device_ms for s in stats)
-        bytes_per_frame = 4 * w * h + 8 * coverage + 8 * w * h + (4 * w * h if mode.endswith("_u8") else 0)
+        bytes_per_frame = 4 * w * h + 8 * coverage + 8 * w * h + (4 * w * h if mode.endswith("_u8") else 0) + (18 * w * h if mode.endswith("_422") else 0)
         result[mode] = {"value": frames / wall, "unit": "frames/s", "wall_ms": wall * 1e3, "slowest_gpu_device_ms": device_ms,
                         "device_fps": frames / (device_ms * 1e-3), "gpu_launches": int(lib.cv_kernel_launches() - before),
                         "frames_per_gpu": [int(s.frames) for s in stats], "algorithmic_gb_per_s": bytes_per_frame * frames / wall / 1e9,
-                        "h2d_bytes_per_frame": (sum(int(s.h2d_bytes) for s in stats) / frames), "d2h_bytes_per_frame": (4 * w * h if mode.endswith("_u8") else 0)}
+                        "h2d_bytes_per_frame": (sum(int(s.h2d_bytes) for s in stats) / frames), "d2h_bytes_per_frame": (4 * w * h if mode.endswith("_u8") else (2 * w * h if mode.endswith("_422") else 0))}
     for k in keep:
         if hasattr(k, "free"):
             try:
