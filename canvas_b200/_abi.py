@@ -206,6 +206,7 @@ _PROTOTYPES = {
     "cv_solid_frame_f16": (C.c_int, [C.POINTER(FrameF16), C.POINTER(Box2i), C.POINTER(C.c_float), C.c_void_p]),
     "cv_solid_frame_f32": (C.c_int, [C.POINTER(FrameF32), C.POINTER(Box2i), C.POINTER(C.c_float), C.c_void_p]),
     "cv_scale_bilinear_f32": (C.c_int, [C.POINTER(FrameF32), V2f, C.POINTER(FrameF32), V2f, V2f, C.c_void_p]),
+    "cv_scale_bilinear_static_f32": (C.c_int, [C.POINTER(FrameF32), V2f, C.POINTER(FrameF32), V2f, V2f, C.c_void_p]),
     "cv_gain_offset_f32": (C.c_int, [C.POINTER(FrameF32), C.c_float, C.c_float, C.c_void_p]),
     "cv_weave_fields_f16": (C.c_int, [C.POINTER(FrameF16), C.POINTER(FrameF16), C.c_void_p]),
     "cv_color_rgb_to_xyz_sdtv": (C.c_int, [C.POINTER(FrameF16), C.c_void_p]),

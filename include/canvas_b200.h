@@ -223,6 +223,22 @@ int cv_solid_frame_f32( rgba_frame_f32 *frame, const box2i *window, const float 
  * target full_window is written (zero where no tap reaches); current_window as the reference computes it. */
 int cv_scale_bilinear_f32( rgba_frame_f32 *target, v2f target_point, const rgba_frame_f32 *source, v2f source_point, v2f factors, cv_stream stream );
 
+/* cv_scale_bilinear_f32 for callers that may not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, same result bits and same current_window as cv_scale_bilinear_f32, but the call allocates nothing
+ * on the device or the host: the tap tables and the intermediate frame between the two passes live in one static
+ * device array of CV_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit (cv_static.cu).
+ * Limits, rejected with CV_ERR_UNSUPPORTED before anything is launched: an intermediate frame of at most
+ * CV_STATIC_MAX_TEMP_PIXELS pixels (1920x1080 fits), at most CV_STATIC_MAX_LINES target lines and
+ * CV_STATIC_MAX_TAPS filter taps per axis.  All calls on a device share the array, which keeps the last call's
+ * contents (everything read from it is written first by the same call, nothing needs clearing); calls that overlap
+ * on the GPU -- two streams, two threads -- RACE: issue one at a time, stream-ordered after the previous one. */
+#define CV_STATIC_SCRATCH_BYTES     37880320u           /* 32 MiB intermediate frame + 2 x (start | src | coef) tap tables */
+#define CV_STATIC_MAX_TEMP_PIXELS   (2u << 20)
+#define CV_STATIC_MAX_LINES         16384u
+#define CV_STATIC_MAX_TAPS          (256u << 10)
+int cv_scale_bilinear_static_f32( rgba_frame_f32 *target, v2f target_point, const rgba_frame_f32 *source, v2f source_point, v2f factors, cv_stream stream );
+
 /* video_filter_gain_offset_gl (src/cprocess/video_filter.c:27-72; a GLSL shader in the reference, no CPU twin):
  * rgb = rgb * gain + offset over current_window, alpha untouched, in place. */
 int cv_gain_offset_f32( rgba_frame_f32 *frame, float gain, float offset, cv_stream stream );

@@ -26,7 +26,7 @@ def declared_functions(header):
     names = set()
     for m in re.finditer(r"^\s*(?:const\s+)?[A-Za-z_][\w\s\*]*?\b(\w+)\s*\([^;{]*\)\s*;", text, flags=re.M):
         line = m.group(0)
-        if "typedef" in line or "static" in line or "(*" in line:
+        if "typedef" in line or re.search(r"\bstatic\b", line) or "(*" in line:      # the keyword, not a name like cv_..._static_f32
             continue
         names.add(m.group(1))
     return names
