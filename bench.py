@@ -739,15 +739,17 @@ def measure_small_kernels(B, seconds=0.15):
     for b in floats + halves:
         b.free()
 
-    # the bilinear scaler (video_scale.c:231-319): 4K f32 -> 1080p f32, both axes (factor 1/2): reads 16 B/px of the source
-    # once per axis pass in the ideal case; algorithmic = source + target
-    src_full, dst_full = (0, 0, w - 1, h - 1), (0, 0, w // 2 - 1, h // 2 - 1)
-    f32 = np.ascontiguousarray(base.view(np.float16).astype(np.float32))
+    # the bilinear scaler (video_scale.c:231-319): 1080p f32 -> 4K f32, both axes (factor 2).  Enlargement, because for
+    # factors below one the reference sizes its intermediate frame with `* factor` (:253-256) and only that share of the
+    # target is computed; algorithmic = source + target, the intermediate frame stays on chip
+    src_full, dst_full = (0, 0, w // 2 - 1, h // 2 - 1), (0, 0, w - 1, h - 1)
+    f32 = np.ascontiguousarray(base.view(np.float16).astype(np.float32)[:h // 2, :w // 2])
     sources = [dev.DeviceFrame32.from_numpy(np.roll(f32, 7 * i, axis=1), src_full, src_full) for i in range(3)]
     targets = [dev.DeviceFrame32(dst_full) for _ in range(3)]
-    zero, half_ = A.V2f(0.0, 0.0), A.V2f(0.5, 0.5)
-    timed("4k_to_1080p_scale_f32", "k_scale_axis x2", "triangle-filter resampling, horizontal then vertical pass", (w * h + (w // 2) * (h // 2)) * 16,
-          lambda i: dev.check(lib.cv_scale_bilinear_f32(C.byref(targets[i].c), zero, C.byref(sources[i].c), zero, half_, B.stream), "cv_scale_bilinear_f32"), 3)
+    zero, twice = A.V2f(0.0, 0.0), A.V2f(2.0, 2.0)
+    timed("1080p_to_4k_scale_f32", "k_scale_fused<0>", "triangle-filter resampling, both passes in one launch (intermediate frame in shared memory, tap tables cached)",
+          (w * h + (w // 2) * (h // 2)) * 16,
+          lambda i: dev.check(lib.cv_scale_bilinear_f32(C.byref(targets[i].c), zero, C.byref(sources[i].c), zero, twice, B.stream), "cv_scale_bilinear_f32"), 3)
     for f in sources + targets:
         f.free()
     return results

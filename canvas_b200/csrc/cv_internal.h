@@ -114,6 +114,25 @@ typedef struct ScaleArgs {
     const int32_t *start, *src; const float *coef;       /* per target line: taps start[t]..start[t+1]-1 */
 } ScaleArgs;
 
+/* both passes in one launch (cv_scale_fused.cu): a block = a TX x TY tile of the target, its slice of the temporary in
+ * shared memory.  Pass 1 fills the temporary (lines1 lines starting at coordinate origin1 along its axis, cross range
+ * cross1 on the other), pass 2 reads it. */
+enum { CV_SCALE_FUSED_TX = 64, CV_SCALE_FUSED_TY = 16,
+       CV_SCALE_FUSED_MAX_TEMP = 3072,      /* pixels of the temporary per tile: 48 KB of shared memory */
+       CV_SCALE_FUSED_MAX_TAPS = 1024 };    /* taps of one pass that a tile's lines may have (staged in shared memory) */
+typedef struct FusedScaleArgs {
+    float4 *target; int32_t t_pitch, t_ox, t_oy; uint32_t t_width, t_height;
+    const float4 *source; int32_t s_pitch, s_ox, s_oy;
+    int32_t x_first;                                     /* 1: horizontal pass first */
+    int32_t origin1, lines1, cross1_lo, cross1_hi;
+    const int32_t *start1, *src1; const float *coef1;
+    int32_t cross2_lo, cross2_hi;
+    const int32_t *start2, *src2; const float *coef2;   /* indexed by target line along the second axis */
+    uint32_t temp_pixels;                                /* largest slice of the temporary any tile needs */
+    float one;                                           /* 1.0f, opaque to the compiler (see tap_accumulate) */
+    uint32_t cap1, cap2;                                 /* most taps of a pass that any tile's lines have, rounded up to 4 */
+} FusedScaleArgs;
+
 typedef struct ColorArgs {
     uint2 *frame; int32_t pitch, ox, oy; DevBox win; uint32_t width, total, magic;
     const uint16_t *pre, *post;                             /* tables applied to all four channels before / after, or NULL */
@@ -221,6 +240,7 @@ CvHostCtx *cvi_host_ctx( void );                                    /* NULL (err
 void *cvi_host_slab( CvHostCtx *ctx, size_t bytes, int *index );    /* pinned staging memory; waits for the slab's previous copy */
 void cvi_host_slab_done( CvHostCtx *ctx, int index );               /* the slab's contents are in flight on ctx->stream */
 void cvi_pool_release_all( int device );
+void cvi_scale_cache_release( int device );                         /* cv_scale.c: cached tap tables go before the pool does */
 
 /* kernels (cv_kernels.cu) */
 int cvi_launch_jobs( int shape, int px /*1|2*/, const DevJob *host_jobs, int count, cudaStream_t stream );
@@ -235,6 +255,7 @@ int cvi_launch_lookup_window( const LookupWindowArgs *args, cudaStream_t stream 
 int cvi_launch_over_f32( const OverF32Args *args, cudaStream_t stream );
 int cvi_launch_fill( const FillArgs *args, cudaStream_t stream );
 int cvi_launch_scale_axis( const ScaleArgs *args, cudaStream_t stream );
+int cvi_launch_scale_fused( const FusedScaleArgs *args, cudaStream_t stream );     /* cv_scale_fused.cu */
 int cvi_launch_gain_offset( const FillArgs *args, cudaStream_t stream );
 int cvi_launch_color( const ColorArgs *args, cudaStream_t stream );
 int cvi_launch_subsample_mpeg2( const Mpeg2Args *args, cudaStream_t stream );

@@ -246,6 +246,7 @@ void cv_shutdown( void ) {
         if( !dev->ready ) continue;
         cudaSetDevice( d );
         cudaDeviceSynchronize();
+        cvi_scale_cache_release( d );
         cvi_pool_release_all( d );
         for( int i = 0; i < CV_LUT_COUNT; i++ ) cudaFree( dev->lut[i] );
         cudaFree( dev->gamma45 );

@@ -15,6 +15,7 @@
 
 #include <limits.h>
 #include <math.h>
+#include <pthread.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -109,13 +110,121 @@ static int plan_axis( AxisPlan *p, float tmin, int t_lo, int t_hi, float smin, i
     return rc;
 }
 
+/* ------------------------------------------------------------- cache of uploaded tap tables */
+
+/*
+ * A video scales every frame of a clip by the same geometry, so the tap tables -- a pure function of the points, the
+ * factors, the source's current window and the target's full window -- are planned and uploaded once and kept in
+ * HBM per device (a few hundred KB each), least recently used of SCALE_CACHE_WAYS replaced.  A hit costs a key
+ * compare and the launch; a miss plans on the host and uploads on the caller's stream (other streams wait on the
+ * entry's `ready` event).  An entry's table may be in use by launches already queued on any stream, so replacing one
+ * synchronises the device first (rare: more than SCALE_CACHE_WAYS geometries in rotation).  The lock is held from
+ * lookup to launch so that no entry is replaced between the two.  CV_NO_SCALE_CACHE=1 turns hits off (for timing
+ * the miss path); cv_shutdown() drops everything (cvi_scale_cache_release).
+ */
+enum { SCALE_CACHE_WAYS = 12, SCALE_KIND_AXIS = 1, SCALE_KIND_FUSED = 2 };
+enum { ENTRY_FREE = 0, ENTRY_READY = 1, ENTRY_NOT_APPLICABLE = 2 };
+
+typedef struct ScaleKey {
+    int32_t kind, order;            /* order: `vertical` for one axis, `x_first` for both */
+    float tp[2], sp[2], factor[2];
+    box2i source_cw, target_full;
+} ScaleKey;
+
+typedef struct ScaleEntry {
+    int state;
+    uint64_t stamp;
+    ScaleKey key;
+    void *table;                    /* pooled device block holding every array the args point into */
+    cudaEvent_t ready;              /* recorded behind the upload */
+    ScaleArgs axis;                 /* templates: frame pointers, pitches and origins are filled in per call */
+    FusedScaleArgs fused;
+    box2i window;                   /* the target's current_window after the launch */
+} ScaleEntry;
+
+static ScaleEntry g_scale_cache[CV_MAX_DEVICES][SCALE_CACHE_WAYS];
+static pthread_mutex_t g_scale_lock = PTHREAD_MUTEX_INITIALIZER;
+static uint64_t g_scale_stamp;
+
+static int cache_enabled( void ) {
+    static int state = -1;
+    if( state < 0 ) { const char *e = getenv( "CV_NO_SCALE_CACHE" ); state = !( e && *e && *e != '0' ); }
+    return state;
+}
+
+static void entry_drop( ScaleEntry *e, int synchronise ) {
+    if( e->state == ENTRY_READY ) {
+        if( synchronise ) cudaDeviceSynchronize();       /* launches queued on any stream may still read the table */
+        if( e->table ) cvi_pool_free( e->table );
+        if( e->ready ) cudaEventDestroy( e->ready );
+    }
+    memset( e, 0, sizeof(*e) );
+}
+
+/* cv_shutdown(), with the device current and idle, before the pool goes */
+void cvi_scale_cache_release( int device ) {
+    if( device < 0 || device >= CV_MAX_DEVICES ) return;
+    pthread_mutex_lock( &g_scale_lock );
+    for( int i = 0; i < SCALE_CACHE_WAYS; i++ )
+        entry_drop( &g_scale_cache[device][i], 0 );
+    pthread_mutex_unlock( &g_scale_lock );
+}
+
+/* with g_scale_lock held: the entry of `key` (state READY / NOT_APPLICABLE) or a cleared slot to fill (state FREE) */
+static ScaleEntry *cache_find( int device, const ScaleKey *key ) {
+    ScaleEntry *set = g_scale_cache[device], *victim = NULL;
+    for( int i = 0; i < SCALE_CACHE_WAYS && cache_enabled(); i++ )
+        if( set[i].state != ENTRY_FREE && !memcmp( &set[i].key, key, sizeof(*key) ) ) {
+            set[i].stamp = ++g_scale_stamp;
+            return &set[i];
+        }
+    for( int i = 0; i < SCALE_CACHE_WAYS && !victim; i++ )
+        if( set[i].state == ENTRY_FREE ) victim = &set[i];
+    for( int i = 0; i < SCALE_CACHE_WAYS && ( !victim || victim->state != ENTRY_FREE ); i++ )
+        if( !victim || set[i].stamp < victim->stamp ) victim = &set[i];
+    entry_drop( victim, 1 );
+    victim->key = *key;
+    victim->stamp = ++g_scale_stamp;
+    return victim;
+}
+
+/* host arrays -> one pooled device block on `stream`; records the entry's ready event */
+static int entry_upload( ScaleEntry *e, const int32_t *host_words, size_t words, cudaStream_t stream ) {
+    int rc = cvi_pool_alloc( &e->table, sizeof(int32_t) * words );
+    if( !rc ) rc = cvi_cuda( cudaMemcpyAsync( e->table, host_words, sizeof(int32_t) * words, cudaMemcpyHostToDevice, stream ), "cudaMemcpyAsync(taps)" );
+    /* the copy reads pageable memory: it has been staged by the time the call returns */
+    if( !rc ) rc = cvi_cuda( cudaEventCreateWithFlags( &e->ready, cudaEventDisableTiming ), "cudaEventCreate" );
+    if( !rc ) rc = cvi_cuda( cudaEventRecord( e->ready, stream ), "cudaEventRecord" );
+    if( rc ) {
+        if( e->table ) cvi_pool_free_async( e->table, stream );
+        if( e->ready ) cudaEventDestroy( e->ready );
+        e->table = NULL; e->ready = NULL;
+    }
+    return rc;
+}
+
 static int imax2( int a, int b ) { return a > b ? a : b; }
 static int imin2( int a, int b ) { return a < b ? a : b; }
+
+/* current_window of an axis pass (video_scale.c:123-140, 224-228) */
+static void window_after( box2i *w, const AxisPlan *plan, int vertical, int cross_lo, int cross_hi ) {
+    if( vertical ) box2i_set( w, cross_lo, plan->used_lo, cross_hi, plan->used_hi );
+    else if( cross_lo <= cross_hi ) box2i_set( w, plan->used_lo, cross_lo, plan->used_hi, cross_hi );
+    else box2i_set( w, INT_MAX, cross_lo, INT_MIN, cross_hi );      /* :139-140 untouched by an empty row loop */
+}
+
+static void key_init( ScaleKey *key, int kind, int order, const box2i *source_cw, const box2i *target_full ) {
+    memset( key, 0, sizeof(*key) );
+    key->kind = kind; key->order = order;
+    key->source_cw = *source_cw; key->target_full = *target_full;
+}
 
 /* one axis: target (whole full_window written) from source->current_window */
 static int scale_axis( rgba_frame_f32 *target, float tmin, const rgba_frame_f32 *source, float smin, float factor, int vertical, cudaStream_t stream ) {
     const box2i s = source->current_window, t = target->full_window;
     const int tw = t.max.x - t.min.x + 1, th = t.max.y - t.min.y + 1;
+    CvDevice *dev = cvi_device();
+    if( !dev ) { box2i_set_empty( &target->current_window ); return CV_ERR_NOT_INITIALISED; }
 
     if( tw <= 0 || th <= 0 ) {
         box2i_set_empty( &target->current_window );
@@ -129,53 +238,225 @@ static int scale_axis( rgba_frame_f32 *target, float tmin, const rgba_frame_f32 
         return cv_copy_frame_alpha_f32( target, source, 1.0f, stream );
     }
 
-    const int cross_lo = vertical ? imax2( s.min.x, t.min.x ) : imax2( s.min.y, t.min.y );
-    const int cross_hi = vertical ? imin2( s.max.x, t.max.x ) : imin2( s.max.y, t.max.y );
+    ScaleKey key;
+    key_init( &key, SCALE_KIND_AXIS, vertical, &s, &t );
+    key.tp[0] = tmin; key.sp[0] = smin; key.factor[0] = factor;
 
-    AxisPlan plan;
-    int rc = vertical ? plan_axis( &plan, tmin, t.min.y, t.max.y, smin, s.min.y, s.max.y, factor )
+    pthread_mutex_lock( &g_scale_lock );
+    ScaleEntry *e = cache_find( dev->index, &key );
+    int rc = CV_OK;
+
+    if( e->state == ENTRY_FREE ) {
+        const int cross_lo = vertical ? imax2( s.min.x, t.min.x ) : imax2( s.min.y, t.min.y );
+        const int cross_hi = vertical ? imin2( s.max.x, t.max.x ) : imin2( s.max.y, t.max.y );
+        AxisPlan plan;
+        rc = vertical ? plan_axis( &plan, tmin, t.min.y, t.max.y, smin, s.min.y, s.max.y, factor )
                       : plan_axis( &plan, tmin, t.min.x, t.max.x, smin, s.min.x, s.max.x, factor );
-    if( rc ) { box2i_set_empty( &target->current_window ); return rc; }
+        if( !rc ) {
+            /* the table travels as one block: [start | src | coef] */
+            const int lines = vertical ? th : tw;
+            const size_t n_start = (size_t) lines + 1, n_taps = (size_t) plan.total + 1;
+            const size_t words = n_start + 2 * n_taps;
+            int32_t *host_table = (int32_t *) malloc( sizeof(int32_t) * words );
+            if( !host_table ) rc = cvi_fail( CV_ERR_MEMORY, "cv_scale_bilinear_f32: out of host memory" );
+            else {
+                memcpy( host_table, plan.start, sizeof(int32_t) * n_start );
+                memcpy( host_table + n_start, plan.src, sizeof(int32_t) * n_taps );
+                memcpy( host_table + n_start + n_taps, plan.coef, sizeof(float) * n_taps );
+                rc = entry_upload( e, host_table, words, stream );
+                free( host_table );
+            }
+            if( !rc ) {
+                ScaleArgs *A = &e->axis;
+                A->t_pitch = tw; A->t_ox = t.min.x; A->t_oy = t.min.y;
+                A->t_width = (uint32_t) tw; A->total = (uint32_t) tw * (uint32_t) th; A->magic = cvi_div_magic( (uint32_t) tw );
+                A->vertical = vertical; A->cross_lo = cross_lo; A->cross_hi = cross_hi;
+                A->start = (const int32_t *) e->table;
+                A->src = A->start + n_start;
+                A->coef = (const float *)( A->src + n_taps );
+                window_after( &e->window, &plan, vertical, cross_lo, cross_hi );
+                e->state = ENTRY_READY;
+            }
+            plan_free( &plan );
+        }
+    }
 
-    /* the table travels through one pooled device block: [start | src | coef] */
-    const int lines = vertical ? th : tw;
-    const size_t n_start = (size_t) lines + 1, n_taps = (size_t) plan.total + 1;
-    const size_t bytes = sizeof(int32_t) * (n_start + n_taps) + sizeof(float) * n_taps;
-    void *dev_table = NULL, *host_table = malloc( bytes );
-    if( !host_table ) { plan_free( &plan ); return cvi_fail( CV_ERR_MEMORY, "cv_scale_bilinear_f32: out of host memory" ); }
-    memcpy( host_table, plan.start, sizeof(int32_t) * n_start );
-    memcpy( (int32_t *) host_table + n_start, plan.src, sizeof(int32_t) * n_taps );
-    memcpy( (int32_t *) host_table + n_start + n_taps, plan.coef, sizeof(float) * n_taps );
-
-    rc = cvi_pool_alloc( &dev_table, bytes );
-    if( !rc ) rc = cvi_cuda( cudaMemcpyAsync( dev_table, host_table, bytes, cudaMemcpyHostToDevice, stream ), "cudaMemcpyAsync(taps)" );
-    /* the copy reads pageable memory: it has been staged by the time the call returns */
-
+    if( !rc ) rc = cvi_cuda( cudaStreamWaitEvent( stream, e->ready, 0 ), "cudaStreamWaitEvent(taps)" );
     if( !rc ) {
-        ScaleArgs A;
-        memset( &A, 0, sizeof(A) );
-        A.target = (float4 *) target->data; A.t_pitch = tw; A.t_ox = t.min.x; A.t_oy = t.min.y;
-        A.t_width = (uint32_t) tw; A.total = (uint32_t) tw * (uint32_t) th; A.magic = cvi_div_magic( (uint32_t) tw );
+        ScaleArgs A = e->axis;
+        A.target = (float4 *) target->data;
         A.source = (const float4 *) source->data;
         A.s_pitch = source->full_window.max.x - source->full_window.min.x + 1;
         A.s_ox = source->full_window.min.x; A.s_oy = source->full_window.min.y;
-        A.vertical = vertical; A.cross_lo = cross_lo; A.cross_hi = cross_hi;
-        A.start = (const int32_t *) dev_table;
-        A.src = A.start + n_start;
-        A.coef = (const float *)( A.src + n_taps );
         rc = cvi_launch_scale_axis( &A, stream );
     }
-
-    if( dev_table )             /* the block returns to the pool once the kernel that reads it has run (stream-ordered) */
-        cvi_pool_free_async( dev_table, stream );
-    free( host_table );
-
     if( rc ) box2i_set_empty( &target->current_window );
-    else if( vertical ) box2i_set( &target->current_window, cross_lo, plan.used_lo, cross_hi, plan.used_hi );
-    else if( cross_lo <= cross_hi ) box2i_set( &target->current_window, plan.used_lo, cross_lo, plan.used_hi, cross_hi );
-    else box2i_set( &target->current_window, INT_MAX, cross_lo, INT_MIN, cross_hi );      /* :139-140 untouched by an empty row loop */
+    else target->current_window = e->window;
+    pthread_mutex_unlock( &g_scale_lock );
+    return rc;
+}
 
-    plan_free( &plan );
+/* ------------------------------------------------------------- both passes in one launch (cv_scale_fused.cu) */
+
+/* The largest slice of the temporary a tile of `per_tile` consecutive second-pass lines reads, in lines of the
+ * temporary; -1 when a tile's taps do not lie between its first and its last one (the kernel's assumption). */
+static int widest_slice( const AxisPlan *p, int lines, int per_tile ) {
+    int widest = 0;
+    for( int t0 = 0; t0 < lines; t0 += per_tile ) {
+        const int t1 = t0 + per_tile < lines ? t0 + per_tile : lines;
+        const int first = p->start[t0], last = p->start[t1];
+        if( first >= last ) continue;
+        int lo = INT_MAX, hi = INT_MIN;
+        for( int i = first; i < last; i++ ) {
+            if( p->src[i] < lo ) lo = p->src[i];
+            if( p->src[i] > hi ) hi = p->src[i];
+        }
+        if( lo != p->src[first] || hi != p->src[last - 1] ) return -1;
+        if( hi - lo + 1 > widest ) widest = hi - lo + 1;
+    }
+    return widest;
+}
+
+/* the most taps any tile's lines have: tiles of `per_tile` lines, the first one starting at line `first_line` of the
+ * plan (negative when the tile grid starts outside the plan's lines) */
+static int most_taps( const AxisPlan *p, int lines, int first_line, int tiled_lines, int per_tile ) {
+    int most = 0;
+    for( int t0 = 0; t0 < tiled_lines; t0 += per_tile ) {
+        int a = first_line + t0, b = first_line + ( t0 + per_tile < tiled_lines ? t0 + per_tile : tiled_lines );
+        if( a < 0 ) a = 0;
+        if( b > lines ) b = lines;
+        if( b > a && p->start[b] - p->start[a] > most ) most = p->start[b] - p->start[a];
+    }
+    return most;
+}
+
+static int fused_enabled( void ) {
+    static int state = -1;
+    if( state < 0 ) { const char *e = getenv( "CV_NO_SCALE_FUSED" ); state = !( e && *e && *e != '0' ); }
+    return state;
+}
+
+/* plans both passes into the entry: 1 = ready, 0 = not applicable, < 0 = error */
+static int fused_build( ScaleEntry *e, const box2i *s, const box2i *t, v2f target_point, v2f source_point, v2f factors,
+                        const box2i *want, int x_first, cudaStream_t stream ) {
+    const int tw = t->max.x - t->min.x + 1, th = t->max.y - t->min.y + 1;
+
+    /* pass 1: source -> temporary (full window `want`); pass 2: temporary -> target */
+    const int vertical1 = !x_first, vertical2 = x_first;
+    const float tmin1 = x_first ? target_point.x : target_point.y, smin1 = x_first ? source_point.x : source_point.y;
+    const float tmin2 = x_first ? target_point.y : target_point.x, smin2 = x_first ? source_point.y : source_point.x;
+    const float factor1 = x_first ? factors.x : factors.y, factor2 = x_first ? factors.y : factors.x;
+    if( ( factor1 == 1.0f && tmin1 == smin1 ) || ( factor2 == 1.0f && tmin2 == smin2 ) ) return 0;      /* a copy pass */
+
+    const int cross1_lo = vertical1 ? imax2( s->min.x, want->min.x ) : imax2( s->min.y, want->min.y );
+    const int cross1_hi = vertical1 ? imin2( s->max.x, want->max.x ) : imin2( s->max.y, want->max.y );
+    AxisPlan plan1, plan2;
+    if( vertical1 ? plan_axis( &plan1, tmin1, want->min.y, want->max.y, smin1, s->min.y, s->max.y, factor1 )
+                  : plan_axis( &plan1, tmin1, want->min.x, want->max.x, smin1, s->min.x, s->max.x, factor1 ) )
+        return 0;                               /* the two-pass path reports it */
+    box2i temp_cw;
+    window_after( &temp_cw, &plan1, vertical1, cross1_lo, cross1_hi );
+    if( box2i_is_empty( &temp_cw ) ) { plan_free( &plan1 ); return 0; }
+
+    const int cross2_lo = vertical2 ? imax2( temp_cw.min.x, t->min.x ) : imax2( temp_cw.min.y, t->min.y );
+    const int cross2_hi = vertical2 ? imin2( temp_cw.max.x, t->max.x ) : imin2( temp_cw.max.y, t->max.y );
+    if( vertical2 ? plan_axis( &plan2, tmin2, t->min.y, t->max.y, smin2, temp_cw.min.y, temp_cw.max.y, factor2 )
+                  : plan_axis( &plan2, tmin2, t->min.x, t->max.x, smin2, temp_cw.min.x, temp_cw.max.x, factor2 ) ) {
+        plan_free( &plan1 );
+        return 0;
+    }
+
+    const int lines1 = vertical1 ? want->max.y - want->min.y + 1 : want->max.x - want->min.x + 1;
+    const int lines2 = vertical2 ? th : tw;
+    const int slice = widest_slice( &plan2, lines2, vertical2 ? CV_SCALE_FUSED_TY : CV_SCALE_FUSED_TX );
+    const long long temp_pixels = (long long) slice * ( vertical2 ? CV_SCALE_FUSED_TX : CV_SCALE_FUSED_TY );
+    /* pass 1 is indexed by the tile's lines along the OTHER axis (rows of the tile for a vertical first pass) */
+    const int taps1 = vertical1 ? most_taps( &plan1, lines1, t->min.y - want->min.y, th, CV_SCALE_FUSED_TY )
+                                : most_taps( &plan1, lines1, t->min.x - want->min.x, tw, CV_SCALE_FUSED_TX );
+    const int taps2 = most_taps( &plan2, lines2, 0, lines2, vertical2 ? CV_SCALE_FUSED_TY : CV_SCALE_FUSED_TX );
+    if( slice < 0 || temp_pixels > CV_SCALE_FUSED_MAX_TEMP || taps1 > CV_SCALE_FUSED_MAX_TAPS || taps2 > CV_SCALE_FUSED_MAX_TAPS ) {
+        plan_free( &plan1 ); plan_free( &plan2 );
+        return 0;
+    }
+
+    /* one block: [start1 | src1 | coef1 | start2 | src2 | coef2] */
+    const size_t n_start1 = (size_t) lines1 + 1, n_taps1 = (size_t) plan1.total + 1;
+    const size_t n_start2 = (size_t) lines2 + 1, n_taps2 = (size_t) plan2.total + 1;
+    const size_t words = n_start1 + 2 * n_taps1 + n_start2 + 2 * n_taps2;
+    int32_t *host_table = (int32_t *) malloc( sizeof(int32_t) * words );
+    int rc = host_table ? CV_OK : cvi_fail( CV_ERR_MEMORY, "cv_scale_bilinear_f32: out of host memory" );
+    if( !rc ) {
+        int32_t *h = host_table;
+        memcpy( h, plan1.start, sizeof(int32_t) * n_start1 ); h += n_start1;
+        memcpy( h, plan1.src, sizeof(int32_t) * n_taps1 ); h += n_taps1;
+        memcpy( h, plan1.coef, sizeof(float) * n_taps1 ); h += n_taps1;
+        memcpy( h, plan2.start, sizeof(int32_t) * n_start2 ); h += n_start2;
+        memcpy( h, plan2.src, sizeof(int32_t) * n_taps2 ); h += n_taps2;
+        memcpy( h, plan2.coef, sizeof(float) * n_taps2 );
+        rc = entry_upload( e, host_table, words, stream );
+        free( host_table );
+    }
+    if( !rc ) {
+        FusedScaleArgs *A = &e->fused;
+        A->t_pitch = tw; A->t_ox = t->min.x; A->t_oy = t->min.y;
+        A->t_width = (uint32_t) tw; A->t_height = (uint32_t) th;
+        A->x_first = x_first;
+        A->origin1 = vertical1 ? want->min.y : want->min.x; A->lines1 = lines1;
+        A->cross1_lo = cross1_lo; A->cross1_hi = cross1_hi;
+        A->cross2_lo = cross2_lo; A->cross2_hi = cross2_hi;
+        const int32_t *d = (const int32_t *) e->table;
+        A->start1 = d; d += n_start1;
+        A->src1 = d; d += n_taps1;
+        A->coef1 = (const float *) d; d += n_taps1;
+        A->start2 = d; d += n_start2;
+        A->src2 = d; d += n_taps2;
+        A->coef2 = (const float *) d;
+        A->temp_pixels = (uint32_t)( temp_pixels > 0 ? temp_pixels : 1 );
+        A->one = 1.0f;
+        A->cap1 = (uint32_t)( ( taps1 + 3 ) & ~3 ); A->cap2 = (uint32_t)( ( taps2 + 3 ) & ~3 );
+        window_after( &e->window, &plan2, vertical2, cross2_lo, cross2_hi );
+    }
+    plan_free( &plan1 ); plan_free( &plan2 );
+    return rc ? rc : 1;
+}
+
+/* 1 = rendered, 0 = not applicable (the caller takes the two-pass path), < 0 = error */
+static int scale_fused( rgba_frame_f32 *target, v2f target_point, const rgba_frame_f32 *source, v2f source_point, v2f factors,
+                        const box2i *want, int x_first, cudaStream_t stream ) {
+    CvDevice *dev = cvi_device();
+    const box2i s = source->current_window, t = target->full_window;
+    if( !dev || !fused_enabled() || t.max.x < t.min.x || t.max.y < t.min.y ) return 0;
+
+    ScaleKey key;
+    key_init( &key, SCALE_KIND_FUSED, x_first, &s, &t );
+    key.tp[0] = target_point.x; key.tp[1] = target_point.y;
+    key.sp[0] = source_point.x; key.sp[1] = source_point.y;
+    key.factor[0] = factors.x; key.factor[1] = factors.y;
+
+    pthread_mutex_lock( &g_scale_lock );
+    ScaleEntry *e = cache_find( dev->index, &key );
+    int rc = 1;
+    if( e->state == ENTRY_FREE ) {
+        rc = fused_build( e, &s, &t, target_point, source_point, factors, want, x_first, stream );
+        if( rc >= 0 ) e->state = rc ? ENTRY_READY : ENTRY_NOT_APPLICABLE;
+    }
+    else if( e->state == ENTRY_NOT_APPLICABLE ) rc = 0;
+
+    if( rc > 0 ) {
+        int err = cvi_cuda( cudaStreamWaitEvent( stream, e->ready, 0 ), "cudaStreamWaitEvent(taps)" );
+        if( !err ) {
+            FusedScaleArgs A = e->fused;
+            A.target = (float4 *) target->data;
+            A.source = (const float4 *) source->data;
+            A.s_pitch = source->full_window.max.x - source->full_window.min.x + 1;
+            A.s_ox = source->full_window.min.x; A.s_oy = source->full_window.min.y;
+            err = cvi_launch_scale_fused( &A, stream );
+        }
+        if( err ) { box2i_set_empty( &target->current_window ); rc = err; }
+        else target->current_window = e->window;
+    }
+    else if( rc < 0 ) box2i_set_empty( &target->current_window );
+    pthread_mutex_unlock( &g_scale_lock );
     return rc;
 }
 
@@ -220,7 +501,10 @@ int cv_scale_bilinear_f32( rgba_frame_f32 *target, v2f target_point, const rgba_
         return CV_OK;
     }
 
-    int rc = cv_frame_alloc_f32( &temp, &want, CV_MEM_DEVICE );
+    int rc = scale_fused( target, target_point, source, source_point, factors, &want, x_first, s );
+    if( rc ) return rc < 0 ? rc : CV_OK;
+
+    rc = cv_frame_alloc_f32( &temp, &want, CV_MEM_DEVICE );
     if( rc ) { box2i_set_empty( &target->current_window ); return rc; }
 
     if( x_first ) {

@@ -74,6 +74,47 @@ def test_scale_host_entry_point_matches_oracle(dev, case):
     check_scaled(got.array, got.current.tuple(), want, False, "host scale %r" % (case,))
 
 
+def test_cached_tap_tables_hits_and_replacement(dev):
+    """cv_scale.c keeps the uploaded tap tables of the last 12 geometries per device: 20 geometries in rotation, three
+    rounds (misses, replacements, then -- for the last 12 -- hits), different source pixels every round, each result
+    against the oracle; then the same geometry on two streams at once."""
+    from canvas_b200 import _abi as A
+    cases = []
+    for i in range(20):
+        fx, fy = (0.4 + 0.13 * i, 2.2 - 0.09 * i) if i % 2 else (1.9 - 0.07 * i, 0.45 + 0.11 * i)
+        cases.append((fx, fy, (1.0 + i, 2.0), (0.5 * i, 1.25), (i, 2, 60 + i, 40), (-3, -2, 90, 70 - i)))
+    for rounds in range(3):
+        for index, case in enumerate(cases):
+            fx, fy, tp, sp, swin, tfull = case
+            src = source_frame(case, seed=1000 * rounds + index)
+            want = O.HostFrame32(tfull)
+            O.oracle().orc_scale_bilinear_f32(C.byref(want.c), tp[0], tp[1], C.byref(src.c), sp[0], sp[1], fx, fy)
+            dsrc = dev.DeviceFrame32.from_numpy(src.array, src.full.tuple(), src.current.tuple())
+            out = dev.DeviceFrame32(tfull)
+            dev.check(dev.lib().cv_memset(out.c.data, 0x33, out.full.width * out.full.height * 16, None), "cv_memset")
+            dev.check(dev.lib().cv_scale_bilinear_f32(C.byref(out.c), A.V2f(*tp), C.byref(dsrc.c), A.V2f(*sp), A.V2f(fx, fy), None), "scale")
+            dev.sync()
+            check_scaled(out.download(), out.current.tuple(), want, False, "round %d %r" % (rounds, case))
+
+    # a table uploaded on one stream and used from another at once: the second stream waits for the upload
+    case = (1.3, 0.7, (2.0, 3.0), (1.5, 0.25), (0, 0, 700, 500), (0, 0, 900, 360))
+    fx, fy, tp, sp, swin, tfull = case
+    src = source_frame(case, seed=5)
+    want = O.HostFrame32(tfull)
+    O.oracle().orc_scale_bilinear_f32(C.byref(want.c), tp[0], tp[1], C.byref(src.c), sp[0], sp[1], fx, fy)
+    dsrc = dev.DeviceFrame32.from_numpy(src.array, src.full.tuple(), src.current.tuple())
+    streams = [C.c_void_p(), C.c_void_p()]
+    outs = [dev.DeviceFrame32(tfull), dev.DeviceFrame32(tfull)]
+    for st in streams:
+        dev.check(dev.lib().cv_stream_create(C.byref(st)), "cv_stream_create")
+    for st, out in zip(streams, outs):
+        dev.check(dev.lib().cv_scale_bilinear_f32(C.byref(out.c), A.V2f(*tp), C.byref(dsrc.c), A.V2f(*sp), A.V2f(fx, fy), st), "scale")
+    for st, out in zip(streams, outs):
+        dev.sync(st)
+        check_scaled(out.download(), out.current.tuple(), want, False, "two streams")
+        dev.lib().cv_stream_destroy(st)
+
+
 def test_scale_1080p_to_4k_and_back_properties(dev):
     """Full-size properties: a constant image stays constant in the interior under 2x enlargement (the triangle taps
     of every target pixel sum to one) and under 1/2 reduction (taps normalised, filter.c:69-75).  The reduction is run
