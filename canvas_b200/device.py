@@ -10,7 +10,7 @@ import numpy as np
 from . import _abi
 from ._abi import (Box2i, FrameF16, FrameF32, Coded, Layer, Source, FrameJob, CanvasError, check,
                    CV_MEM_DEVICE, CV_LAYOUT_PLANAR, CV_LAYOUT_UYVY, CV_LAYOUT_YUY2, CV_MATRIX_709, CV_MATRIX_601,
-                   CV_SRC_NONE, CV_SRC_F16, CV_SRC_CODED, CV_SRC_F32, CV_MAX_LAYERS)
+                   CV_SRC_NONE, CV_SRC_F16, CV_SRC_CODED, CV_SRC_F32, CV_MAX_LAYERS, LayerOps, CV_OP_WEAVE, CV_OP_GAIN_OFFSET)
 
 _initialised = set()
 
@@ -224,15 +224,27 @@ def _source(obj):
 
 
 def make_job(out=None, a=None, b=None, mix_b=0.0, layers=(), out_f32=None, out_u8=None, u8_table=None, full=None):
-    """Builds a cv_frame_job.  layers: DeviceFrame16 or (DeviceFrame16, mix) bottom -> top."""
+    """Builds a cv_frame_job.  layers: DeviceFrame16, (DeviceFrame16, mix) or (DeviceFrame16, mix, ops) bottom -> top;
+    ops = dict(gain=, offset=, weave=DeviceFrame16 supplying the even rows) or None: the layer's fused filters (cv_layer_ops)."""
     job = FrameJob()
     job.a, job.b, job.mix_b = _source(a), _source(b), mix_b
     if len(layers) > CV_MAX_LAYERS:
         raise ValueError("a frame job fuses at most %d layers" % CV_MAX_LAYERS)
     job.layer_count = len(layers)
+    keep_ops = []
     for i, entry in enumerate(layers):
-        frame, mix = entry if isinstance(entry, tuple) else (entry, 1.0)
+        frame, mix, ops = (tuple(entry) + (None,))[:3] if isinstance(entry, tuple) else (entry, 1.0, None)
         job.layers[i].frame, job.layers[i].mix = frame.c, mix
+        if ops:
+            o = LayerOps()
+            if "gain" in ops:
+                o.flags |= CV_OP_GAIN_OFFSET
+                o.gain, o.offset = ops["gain"], ops.get("offset", 0.0)
+            if ops.get("weave") is not None:
+                o.flags |= CV_OP_WEAVE
+                o.even_rows = ops["weave"].c
+            job.layers[i].ops = C.pointer(o)
+            keep_ops.append((o, ops))
     if out is not None:
         job.out = C.pointer(out.c)
     if out_f32 is not None:
@@ -242,7 +254,7 @@ def make_job(out=None, a=None, b=None, mix_b=0.0, layers=(), out_f32=None, out_u
         job.u8_table = u8_table.ptr if isinstance(u8_table, DeviceBuffer) else u8_table
     if full is not None:
         job.full_window = Box2i(*full)
-    job._keep = (out, out_f32, a, b, layers, out_u8, u8_table)
+    job._keep = (out, out_f32, a, b, layers, out_u8, u8_table, keep_ops)
     return job
 
 

@@ -253,11 +253,23 @@ class _ForeignFrameFunction:
 # ----------------------------------------------------------------------------- descriptions
 
 class _Desc:
-    """What a source contributes at one frame: kind in {'f16', 'f32', 'coded', 'cross', 'stack'} (None = nothing)."""
-    __slots__ = ("kind", "frame", "a", "b", "mix", "layers")
+    """What a source contributes at one frame: kind in {'f16', 'f32', 'coded', 'cross', 'stack'} (None = nothing).
+    An 'f16' leaf may carry `ops`: per-pixel filters still to be applied to it (gain/offset, the field weave) -- evaluated
+    inside the launch that consumes the frame when it ends up as a workspace layer (cv_layer_ops), else by _plain()."""
+    __slots__ = ("kind", "frame", "a", "b", "mix", "layers", "ops")
 
-    def __init__(self, kind, frame=None, a=None, b=None, mix=0.0, layers=()):
-        self.kind, self.frame, self.a, self.b, self.mix, self.layers = kind, frame, a, b, mix, list(layers)
+    def __init__(self, kind, frame=None, a=None, b=None, mix=0.0, layers=(), ops=None):
+        self.kind, self.frame, self.a, self.b, self.mix, self.layers, self.ops = kind, frame, a, b, mix, list(layers), ops
+
+    def layer(self):
+        """this f16 leaf as an entry of make_job(layers=...)"""
+        return (self.frame, 1.0, self.ops) if self.ops else self.frame
+
+
+def _fuse_filters():
+    """CV_PY_NO_FUSED_FILTERS=1 keeps the per-pixel filters as separate passes (for A/B tests)"""
+    import os
+    return os.environ.get("CV_PY_NO_FUSED_FILTERS", "0") in ("", "0")
 
 
 def _flat(window):
@@ -267,7 +279,7 @@ def _flat(window):
 def _leaf(desc, full):
     """A description usable as a bottom source of one job: leaves stay, composites are rendered to f32 first
     (the reference pulls nested filters through get_frame_32, main.c:106-145: no rounding in between)."""
-    if desc is None or desc.kind in ("f16", "f32", "coded"):
+    if desc is None or (desc.kind in ("f16", "f32", "coded") and not desc.ops):
         return desc
     out = dev.DeviceFrame32(full)
     _run(desc, full, out_f32=out)
@@ -284,15 +296,18 @@ def _run(desc, full, out=None, out_f32=None):
         bottom, layers = desc.a, desc.layers
         # fused when everything above the bottom is a plain f16 frame (cv_frame_job's shape)
         if all(l is not None and l.kind == "f16" for l in layers) and len(layers) <= _abi.CV_MAX_LAYERS:
+            entries = [l.layer() for l in layers]
+            if bottom is not None and bottom.kind == "f16" and bottom.ops and len(entries) < _abi.CV_MAX_LAYERS:
+                # a filtered bottom frame: the first layer of a layers-only job (copied with its filters applied)
+                entries, bottom = [bottom.layer()] + entries, None
             bottom = bottom if (bottom is None or bottom.kind != "stack") else _leaf(bottom, full)
             a, b, mix = (bottom.a, bottom.b, bottom.mix) if bottom is not None and bottom.kind == "cross" else (bottom, None, 0.0)
             a, b = _leaf(a, full), _leaf(b, full)
-            job = dev.make_job(out=out, out_f32=out_f32, a=a.frame if a else None, b=b.frame if b else None, mix_b=mix,
-                               layers=[l.frame for l in layers])
+            job = dev.make_job(out=out, out_f32=out_f32, a=a.frame if a else None, b=b.frame if b else None, mix_b=mix, layers=entries)
             if bottom is not None and bottom.kind == "cross" and (a is None or b is None):
                 # video_mix_cross_f32 with one side empty is copy_frame_alpha of the other (video_mix.c:111-118):
                 # keep both slots so the library applies the same rule
-                job = _cross_job(out, out_f32, a, b, mix, full, [l.frame for l in layers])
+                job = _cross_job(out, out_f32, a, b, mix, full, entries)
             dev.render_frames([job])
             target.c.current_window = job.current_window
             return
@@ -316,7 +331,10 @@ def _run(desc, full, out=None, out_f32=None):
         dev.render_frames([job])
         target.c.current_window = job.current_window
         return
-    job = dev.make_job(out=out, out_f32=out_f32, a=desc.frame)
+    if desc.ops:       # a filtered frame on its own: a one-layer job, the filters run inside it
+        job = dev.make_job(out=out, out_f32=out_f32, layers=[desc.layer()])
+    else:
+        job = dev.make_job(out=out, out_f32=out_f32, a=desc.frame)
     dev.render_frames([job])
     target.c.current_window = job.current_window
 
@@ -674,8 +692,14 @@ class VideoGainOffsetFilter(VideoSource):
     def _describe(self, frame_index, full):
         if self.source is None:
             return None
+        inner = _describe_of(self.source, frame_index, full)
+        if inner is not None and inner.kind == "f16" and not (inner.ops and "gain" in inner.ops) and _fuse_filters():
+            # an f16 frame: the filter rides on it and is evaluated in f32 inside the launch that consumes the frame
+            # (cv_layer_ops; the same bits as the separate pass below, tests/test_gpu_layer_ops.py)
+            ops = dict(inner.ops or {}, gain=self._gain.f32(frame_index), offset=self._offset.f32(frame_index))
+            return _Desc("f16", inner.frame, ops=ops)
         frame = dev.DeviceFrame32(full)
-        _run(_describe_of(self.source, frame_index, full), full, out_f32=frame)
+        _run(inner, full, out_f32=frame)
         if frame.current.empty:
             return None
         check(dev.lib().cv_gain_offset_f32(C.byref(frame.c), self._gain.f32(frame_index), self._offset.f32(frame_index), None),
@@ -697,8 +721,21 @@ class Pulldown23RemovalFilter(VideoSource):
         base = ((frame_index + self.offset) >> 2) * 5 - self.offset
         if phase != 2:
             return _describe_of(self.source, base + {0: 0, 1: 1, 3: 4}[phase], full)
+        first = _describe_of(self.source, base + 2, full)
+        if first is not None and first.kind == "f16" and not first.ops and _fuse_filters():
+            # both fields are plain f16 frames: the weave becomes a row-parity select on the layer's pointer inside the
+            # consuming launch -- when the second frame defines every pixel the first one contributes
+            second = _describe_of(self.source, base + 3, full)
+            if second is not None and second.kind == "f16" and not second.ops:
+                box = _box(full)
+                clip = lambda w: (max(w[0], box.min.x), max(w[1], box.min.y), min(w[2], box.max.x), min(w[3], box.max.y))
+                a, b = clip(first.frame.current.tuple()), clip(second.frame.current.tuple())
+                if a[2] < a[0] or a[3] < a[1]:
+                    return None
+                if b[0] <= a[0] and b[1] <= a[1] and b[2] >= a[2] and b[3] >= a[3]:
+                    return _Desc("f16", first.frame, ops={"weave": second.frame})
         frame = dev.DeviceFrame16(full)
-        _run(_describe_of(self.source, base + 2, full), full, out=frame)
+        _run(first, full, out=frame)
         if frame.current.empty:
             return None
         window = frame.current.tuple()

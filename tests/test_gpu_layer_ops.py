@@ -194,3 +194,56 @@ def test_batch_of_filtered_frames_is_one_launch(gpu):
     assert dev.lib().cv_kernel_launches() - before == 1
     for out, want in zip(outs, wants):
         assert np.array_equal(out.download(), want.array)
+
+
+def test_python_filters_ride_on_workspace_layers(gpu, monkeypatch):
+    """fluggo.media.process level: VideoGainOffsetFilter and the weaving frame of Pulldown23RemovalFilter over f16 frames
+    inside a VideoWorkspace are evaluated inside the ONE composite launch (cv_layer_ops); the result has the bits of the
+    same graph with the filters as separate passes (CV_PY_NO_FUSED_FILTERS=1), as f16 and as f32, and on their own."""
+    A, dev = gpu
+    from canvas_b200 import process
+    from canvas_b200.basetypes import box2i
+    full = (0, -1, 95, 46)
+    for weave_fits in (True, False):
+        check_python_filter_graph(dev, monkeypatch, full, weave_fits)
+
+
+def check_python_filter_graph(dev, monkeypatch, full, weave_fits):
+    """weave_fits: the frame that supplies the even rows (clip frame 3) defines every pixel of the woven one (clip frame 2),
+    so the weave can ride on the layer; otherwise that filter stays a separate pass (and the results still agree)"""
+    from canvas_b200 import process
+    from canvas_b200.basetypes import box2i
+    partial = (8, 3, 90, 40)
+    frames = [O.synth_frame(full, 1200 + i, partial if i % 3 == (2 if weave_fits else 0) else full) for i in range(10)]
+
+    class Clip(process.VideoSource):
+        def _describe(self, frame_index, window):
+            f = frames[frame_index % len(frames)]
+            return process.RgbaFrameF16(f.full.tuple(), f.current.tuple(), f.array)._describe(frame_index, window)
+
+    def graph():
+        ws = process.VideoWorkspace()
+        bottom = O.synth_frame(full, 77, full)
+        ws.add(source=process.RgbaFrameF16(full, full, bottom.array), x=0, length=100, z=0)
+        ws.add(source=process.VideoGainOffsetFilter(Clip(), 1.5, -0.125), x=0, length=100, z=1)
+        # output frame 2 with offset 0 is the weaving phase (frames 2 and 3 of the clip); gain/offset on top of the weave
+        ws.add(source=process.VideoGainOffsetFilter(process.Pulldown23RemovalFilter(Clip(), 0), 0.75, 0.0625), x=0, length=100, z=2)
+        return ws
+
+    results = {}
+    for fused in (True, False):
+        monkeypatch.setenv("CV_PY_NO_FUSED_FILTERS", "0" if fused else "1")
+        ws = graph()
+        before = dev.lib().cv_kernel_launches()
+        f16 = ws.get_frame_f16(2, box2i(*full))
+        launches = dev.lib().cv_kernel_launches() - before
+        f32 = ws.get_frame_f32(2, box2i(*full))
+        alone = process.VideoGainOffsetFilter(process.Pulldown23RemovalFilter(Clip(), 0), 0.75, 0.0625).get_frame_f16(2, box2i(*full))
+        results[fused] = (f16, f32, alone, launches)
+    (a16, a32, aalone, fused_launches), (b16, b32, balone, separate_launches) = results[True], results[False]
+    assert separate_launches > 3 and (fused_launches == 1 if weave_fits else fused_launches > 1)
+    for x, y in ((a16, b16), (a32, b32), (aalone, balone)):
+        assert x.current_window.flat() == y.current_window.flat()
+        x0, y0, x1, y1 = x.current_window.flat()
+        xs, ys = slice(x0 - full[0], x1 - full[0] + 1), slice(y0 - full[1], y1 - full[1] + 1)
+        assert np.array_equal(np.asarray(x.data)[ys, xs].view(np.uint8), np.asarray(y.data)[ys, xs].view(np.uint8))
