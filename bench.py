@@ -654,6 +654,14 @@ def plugin_e2e(B, name, sets, check=True):
     result = {"value": dist_sum(B.dist, float(count)) / seconds, "unit": "frames/s", "threads": threads, "frames_timed": count,
               "call": "video_get_frame_f16(workspace_as_video_source(...), frame, &host_frame) over %d host-frame sources per frame "
                       "(include/framework.h; pageable host memory in and out)" % n_layers}
+    # what the host itself can copy: each output frame costs n_layers + 1 whole-frame memcpys on the CPU (every source
+    # writes its frame into the caller's buffer; the result is copied into the caller's frame)
+    if B.rank == 0:
+        client.client_host_copy_rate.restype = C.c_double
+        client.client_host_copy_rate.argtypes = [C.c_int, C.c_size_t, C.c_int]
+        rate = client.client_host_copy_rate(threads, w * h * 8, 6)
+        result["host_copy_gbs"] = rate / 1e9
+        result["host_copy_bound_fps"] = rate / ((n_layers + 1) * w * h * 8) if rate else None
     if check:
         one = A.FrameF16()
         got = np.zeros((h, w, 4), np.uint16)

@@ -17,6 +17,7 @@
 
 #include <pthread.h>
 #include <stdlib.h>
+#include <string.h>
 #include <time.h>
 
 /* ---- host frames as sources ---------------------------------------------------------------- */
@@ -185,4 +186,44 @@ EXPORT int64_t client_time_timeline( client_timeline *tl, int first_frame, int c
     free( ids );
     free( workers );
     return elapsed;
+}
+
+/* ------------------------------------------------------------- host copy rate (a diagnostic for bench.py)
+ *
+ * Every frame a host-frame source hands over is a memcpy of the whole frame into the caller's buffer: the plug-in
+ * path of a workspace over N such sources moves N + 1 frames through the CPU per output frame, whatever the GPU
+ * does.  This measures what `threads` threads copying `bytes`-sized pageable buffers at once achieve on this host,
+ * so that the e2e_plugin figure can be read against it. */
+typedef struct copy_worker { unsigned char *from, *to; size_t bytes; int repeats; } copy_worker;
+
+static void *copy_thread( void *arg ) {
+    copy_worker *w = (copy_worker *) arg;
+    for( int i = 0; i < w->repeats; i++ )
+        memcpy( w->to, w->from, w->bytes );
+    return NULL;
+}
+
+/* returns the copy rate in bytes copied per second over all threads (0 on allocation failure) */
+EXPORT double client_host_copy_rate( int threads, size_t bytes, int repeats ) {
+    pthread_t *ids = (pthread_t *) calloc( (size_t) threads, sizeof(pthread_t) );
+    copy_worker *workers = (copy_worker *) calloc( (size_t) threads, sizeof(copy_worker) );
+    int ok = ids && workers;
+    for( int t = 0; t < threads && ok; t++ ) {
+        workers[t].from = (unsigned char *) malloc( bytes );
+        workers[t].to = (unsigned char *) malloc( bytes );
+        workers[t].bytes = bytes; workers[t].repeats = repeats;
+        ok = workers[t].from && workers[t].to;
+        if( ok ) { memset( workers[t].from, t + 1, bytes ); memset( workers[t].to, 0, bytes ); }     /* pages touched */
+    }
+    double rate = 0.0;
+    if( ok ) {
+        const int64_t begin = now_ns();
+        for( int t = 0; t < threads; t++ ) pthread_create( &ids[t], NULL, copy_thread, &workers[t] );
+        for( int t = 0; t < threads; t++ ) pthread_join( ids[t], NULL );
+        const int64_t elapsed = now_ns() - begin;
+        rate = (double) bytes * repeats * threads / ( (double) elapsed * 1e-9 );
+    }
+    for( int t = 0; t < threads && workers; t++ ) { free( workers[t].from ); free( workers[t].to ); }
+    free( ids ); free( workers );
+    return rate;
 }

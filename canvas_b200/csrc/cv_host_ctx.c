@@ -7,7 +7,7 @@
  * for another thread's work: a pull from the widget thread and the pull queue's two threads overlap their copies and
  * kernels on the device instead of queueing behind one shared stream.
  *
- *   - the slabs are where pulled sources write their pixels (video_get_frame_f16(source, ..., &frame_in_slab)), so the
+ *   - the slabs (pinned blocks from the pool of cv_memory.c, returned to it when the thread ends) are where pulled sources write their pixels (video_get_frame_f16(source, ..., &frame_in_slab)), so the
  *     host->device copy that follows is a true asynchronous DMA out of pinned memory and the thread goes on pulling the
  *     next layer while it runs; a slab is reused only after the event recorded behind its last copy has completed;
  *   - device frames come from the per-device pool and go back to it stream-ordered (cvi_pool_free_async), so a block
@@ -28,7 +28,7 @@ static void ctx_destroy( void *p ) {
     if( cudaSetDevice( ctx->device ) == cudaSuccess ) {
         if( ctx->stream ) cudaStreamSynchronize( ctx->stream );
         for( int i = 0; i < CV_HOST_SLABS; i++ ) {
-            if( ctx->slab[i].ptr ) cudaFreeHost( ctx->slab[i].ptr );
+            if( ctx->slab[i].ptr ) cvi_pinned_free( ctx->slab[i].ptr );       /* back to the pool: the next thread's first pull finds it */
             if( ctx->slab[i].done ) cudaEventDestroy( ctx->slab[i].done );
         }
         if( ctx->stream ) cudaStreamDestroy( ctx->stream );
@@ -74,12 +74,14 @@ void *cvi_host_slab( CvHostCtx *ctx, size_t bytes, int *index ) {
         ctx->slab[i].busy = 0;
     }
     if( ctx->slab[i].bytes < bytes ) {
-        if( ctx->slab[i].ptr ) cudaFreeHost( ctx->slab[i].ptr );
+        if( ctx->slab[i].ptr ) cvi_pinned_free( ctx->slab[i].ptr );
         ctx->slab[i].ptr = NULL;
         ctx->slab[i].bytes = 0;
-        /* grown in 1 MiB steps so that frames of one size share slabs */
+        /* from the pool of pinned blocks (cv_memory.c), which outlives the thread: pinning 66 MB costs milliseconds and
+         * serialises in the driver, and callers with short-lived threads would otherwise pay it on every first pull.
+         * Grown in 1 MiB steps so that frames of one size share slabs */
         const size_t want = (bytes + ((size_t) 1 << 20) - 1) & ~(((size_t) 1 << 20) - 1);
-        if( cvi_cuda( cudaMallocHost( &ctx->slab[i].ptr, want ), "cudaMallocHost(staging slab)" ) ) {
+        if( cvi_pinned_alloc( &ctx->slab[i].ptr, want ) ) {
             ctx->slab[i].ptr = NULL;
             return NULL;
         }

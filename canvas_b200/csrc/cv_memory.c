@@ -212,12 +212,20 @@ void cvi_pinned_free( void *ptr ) {
 }
 
 void cvi_pinned_release_all( void ) {
+    /* blocks in use belong to live per-thread contexts (their staging slabs): they stay listed and are pooled again
+     * when their thread ends */
     pthread_mutex_lock( &g_pinned_lock );
-    for( int i = 0; i < g_pinned_count; i++ )
-        cudaFreeHost( g_pinned[i].ptr );
-    free( g_pinned );
-    g_pinned = NULL;
-    g_pinned_count = g_pinned_capacity = 0;
+    int kept = 0;
+    for( int i = 0; i < g_pinned_count; i++ ) {
+        if( g_pinned[i].in_use ) g_pinned[kept++] = g_pinned[i];
+        else cudaFreeHost( g_pinned[i].ptr );
+    }
+    g_pinned_count = kept;
+    if( !kept ) {
+        free( g_pinned );
+        g_pinned = NULL;
+        g_pinned_capacity = 0;
+    }
     pthread_mutex_unlock( &g_pinned_lock );
 }
 
