@@ -971,6 +971,7 @@ def run_ours(args):
             for s in osets:
                 s.free()
         line["other_workloads"] = others
+    if not args.no_others or args.only_kernels:
         line["other_kernels"] = measure_small_kernels(B)
 
     # ---- the frame-parallel scheduler itself: ONE cv_timeline_render() call over all the GPUs of the job -------------
@@ -1162,6 +1163,7 @@ def main():
     ap.add_argument("--workload", default="4k_8layer_composite", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-others", action="store_true", help="skip the other_workloads array")
+    ap.add_argument("--only-kernels", action="store_true", help="with --no-others: still measure the other_kernels array")
     ap.add_argument("--no-check", action="store_true", help="skip the oracle comparison after the timed region")
     ap.add_argument("--no-numa", action="store_true", help="do not pin the process to the GPU's NUMA node")
     ap.add_argument("--no-plugin", action="store_true", help="skip e2e_plugin (the framework.h pull with host frames)")
