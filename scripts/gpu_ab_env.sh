@@ -1,7 +1,7 @@
 #!/bin/bash
 # scripts/gpu_ab_env.sh "ENV=.. ENV=.." WORKLOAD...   -- same library, with and without the environment settings, two passes
 envs=$1; shift
-run() { env $2 python bench.py --workload $1 --steps 8 --no-others --no-cpu-baseline 2>&1 | python -c "
+run() { env $2 python bench.py --workload $1 --steps 8 --no-others --no-cpu-baseline --no-plugin --no-scheduler 2>&1 | python -c "
 import sys,json
 for l in sys.stdin:
     if l.startswith('{'):
