@@ -390,28 +390,49 @@ static int render_jobs( cv_frame_job *jobs, int count, const BuildOptions *opt, 
         return cvi_launch_jobs( shape, px, &dj, 1, s );
     }
 
-    /* group by (shape, px): jobs are independent, so their order inside the stream is free */
-    DevJob *built = (DevJob *) malloc( sizeof(DevJob) * (size_t) count );
-    DevJob *group = (DevJob *) malloc( sizeof(DevJob) * (size_t) count );
-    int *key = (int *) malloc( sizeof(int) * (size_t) count );
-    if( !built || !group || !key ) {
-        free( built ); free( group ); free( key );
+    /* Built and launched in chunks of RENDER_CHUNK jobs: the device starts on the first chunk while the host builds the
+     * next, and the two scratch arrays stay small enough (3 MB) for the allocator to reuse them without fresh pages -- a
+     * 12 000-job call used to build 36 MB of descriptors before its first launch, which made small frames host-bound.
+     * Inside a chunk jobs are grouped by (shape, px): they are independent, so their order inside the stream is free. */
+    enum { RENDER_CHUNK = 1024 };            /* a multiple of the job ring's segment (256 jobs = one launch) */
+    const int chunk = count < RENDER_CHUNK ? count : RENDER_CHUNK;
+    DevJob *built = (DevJob *) malloc( sizeof(DevJob) * (size_t) chunk );
+    DevJob *group = NULL;
+    int *key = (int *) malloc( sizeof(int) * (size_t) chunk );
+    if( !built || !key ) {
+        free( built ); free( key );
         return cvi_fail( CV_ERR_MEMORY, "cv_render_frames: out of host memory" );
     }
 
     int rc = CV_OK;
-    for( int i = 0; i < count && !rc; i++ ) {
-        int shape = 0, px = 1;
-        rc = build_job( &jobs[i], opt, &built[i], &shape, &px );
-        key[i] = built[i].total_items ? shape * 2 + (px == 2) : -1;
-    }
+    for( int base = 0; base < count && !rc; base += chunk ) {
+        const int m = count - base < chunk ? count - base : chunk;
+        int first_key = -2, mixed = 0;
+        for( int i = 0; i < m && !rc; i++ ) {
+            int shape = 0, px = 1;
+            rc = build_job( &jobs[base + i], opt, &built[i], &shape, &px );
+            key[i] = built[i].total_items ? shape * 2 + (px == 2) : -1;
+            if( first_key == -2 ) first_key = key[i];
+            else if( key[i] != first_key ) mixed = 1;
+        }
+        if( rc ) break;
 
-    for( int k = 0; k < KB_COUNT * 2 && !rc; k++ ) {
-        int n = 0;
-        for( int i = 0; i < count; i++ )
-            if( key[i] == k ) group[n++] = built[i];
-        if( n )
-            rc = cvi_launch_jobs( k / 2, (k & 1) ? 2 : 1, group, n, s );
+        if( !mixed ) {                          /* the usual case: one kind of job, launched from where it was built */
+            if( first_key >= 0 )
+                rc = cvi_launch_jobs( first_key / 2, (first_key & 1) ? 2 : 1, built, m, s );
+            continue;
+        }
+        if( !group && !( group = (DevJob *) malloc( sizeof(DevJob) * (size_t) chunk ) ) ) {
+            rc = cvi_fail( CV_ERR_MEMORY, "cv_render_frames: out of host memory" );
+            break;
+        }
+        for( int k = 0; k < KB_COUNT * 2 && !rc; k++ ) {
+            int n = 0;
+            for( int i = 0; i < m; i++ )
+                if( key[i] == k ) group[n++] = built[i];
+            if( n )
+                rc = cvi_launch_jobs( k / 2, (k & 1) ? 2 : 1, group, n, s );
+        }
     }
 
     free( built ); free( group ); free( key );
