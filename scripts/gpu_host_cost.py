@@ -50,3 +50,25 @@ host = time.perf_counter() - t0
 dev.sync(B.stream)
 total = time.perf_counter() - t0
 print("tiny frames (%dx%d conversions): host %.2f us/job to enqueue, %.2f us/job until done" % (w, h, host * 1e6 / (4 * count), total * 1e6 / (4 * count)))
+
+# the same for windowed layer stacks (k_rect: the host plans rectangles of constant coverage)
+w, h, count = 256, 32, 4096
+full = (0, 0, w - 1, h - 1)
+wins = [full, (16, 4, 200, 28), (64, 0, 255, 20), (0, 10, 127, 31)]
+layers = [[dev.DeviceFrame16(full, current=win) for win in wins] for _ in range(4)]
+for group in layers:
+    for f in group:
+        f.fill(0x3C)
+outs = [dev.DeviceFrame16(full) for _ in range(4)]
+small = [dev.make_job(out=outs[i % 4], layers=layers[i % 4]) for i in range(count)]
+arr = (dev.FrameJob * count)(*small)
+for _ in range(2):
+    dev.check(lib.cv_render_frames(arr, count, B.stream), "render")
+dev.sync(B.stream)
+t0 = time.perf_counter()
+for _ in range(4):
+    dev.check(lib.cv_render_frames(arr, count, B.stream), "render")
+host = time.perf_counter() - t0
+dev.sync(B.stream)
+total = time.perf_counter() - t0
+print("tiny frames (%dx%d, 4 windowed layers): host %.2f us/job to enqueue, %.2f us/job until done" % (w, h, host * 1e6 / (4 * count), total * 1e6 / (4 * count)))

@@ -115,6 +115,43 @@ def test_cached_tap_tables_hits_and_replacement(dev):
         dev.lib().cv_stream_destroy(st)
 
 
+def test_fused_scaler_equals_two_pass_on_random_geometries(dev):
+    """k_scale_fused (one launch, intermediate frame in shared memory) against the two-pass form -- which
+    cv_scale_bilinear_static_f32 still is -- and against the oracle: 60 random geometries (factors 0.15 .. 5 per axis,
+    fractional points, source windows inside larger frames, negative origins, targets that the image only partly covers)"""
+    from canvas_b200 import _abi as A
+    rng = np.random.default_rng(20260)
+    fused_launches = 0
+    for index in range(60):
+        fx, fy = (float(np.float32(np.exp(rng.uniform(np.log(0.15), np.log(5.0))))) for _ in range(2))
+        sw, sh = int(rng.integers(8, 400)), int(rng.integers(6, 240))
+        sx0, sy0 = int(rng.integers(-50, 50)), int(rng.integers(-50, 50))
+        swin = (sx0, sy0, sx0 + sw - 1, sy0 + sh - 1)
+        sp = (float(np.float32(sx0 + rng.uniform(0, sw))), float(np.float32(sy0 + rng.uniform(0, sh))))
+        tw, th = int(rng.integers(8, 500)), int(rng.integers(6, 300))
+        tx0, ty0 = int(rng.integers(-60, 60)), int(rng.integers(-60, 60))
+        tfull = (tx0, ty0, tx0 + tw - 1, ty0 + th - 1)
+        tp = (float(np.float32(tx0 + rng.uniform(0, tw))), float(np.float32(ty0 + rng.uniform(0, th))))
+        case = (fx, fy, tp, sp, swin, tfull)
+        src = source_frame(case, seed=7000 + index)
+        want = O.HostFrame32(tfull)
+        O.oracle().orc_scale_bilinear_f32(C.byref(want.c), tp[0], tp[1], C.byref(src.c), sp[0], sp[1], fx, fy)
+        dsrc = dev.DeviceFrame32.from_numpy(src.array, src.full.tuple(), src.current.tuple())
+        results = []
+        for entry in ("cv_scale_bilinear_f32", "cv_scale_bilinear_static_f32"):
+            out = dev.DeviceFrame32(tfull)
+            dev.check(dev.lib().cv_memset(out.c.data, 0x5A, out.full.width * out.full.height * 16, None), "cv_memset")
+            before = dev.lib().cv_kernel_launches()
+            dev.check(getattr(dev.lib(), entry)(C.byref(out.c), A.V2f(*tp), C.byref(dsrc.c), A.V2f(*sp), A.V2f(fx, fy), None), entry)
+            dev.sync()
+            if entry == "cv_scale_bilinear_f32" and dev.lib().cv_kernel_launches() - before == 1:
+                fused_launches += 1
+            check_scaled(out.download(), out.current.tuple(), want, False, "%s %r" % (entry, case))
+            results.append((out.current.tuple(), out.download()))
+        assert np.array_equal(results[0][1].view(np.uint32), results[1][1].view(np.uint32)), case
+    assert fused_launches >= 15          # the others: strong reductions whose tiles do not fit, empty results
+
+
 def test_scale_1080p_to_4k_and_back_properties(dev):
     """Full-size properties: a constant image stays constant in the interior under 2x enlargement (the triangle taps
     of every target pixel sum to one) and under 1/2 reduction (taps normalised, filter.c:69-75).  The reduction is run
