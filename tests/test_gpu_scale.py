@@ -152,6 +152,47 @@ def test_fused_scaler_equals_two_pass_on_random_geometries(dev):
     assert fused_launches >= 15          # the others: strong reductions whose tiles do not fit, empty results
 
 
+def test_scaler_from_four_threads_with_more_geometries_than_the_cache_holds(dev):
+    """four host threads, a stream each, 16 geometries in different orders (the cache of uploaded tap tables holds 12 per
+    device: hits, misses and replacements interleave); every result against the oracle"""
+    import threading
+    from canvas_b200 import _abi as A
+    cases, wants, sources = [], [], []
+    for i in range(16):
+        fx, fy = (0.5 + 0.2 * i, 2.6 - 0.12 * i)
+        case = (fx, fy, (2.0 + i, 1.0), (0.25 * i, 3.5), (i, 1, 90 + i, 60), (-2, -3, 120, 80 + i))
+        src = source_frame(case, seed=300 + i)
+        want = O.HostFrame32(case[5])
+        O.oracle().orc_scale_bilinear_f32(C.byref(want.c), case[2][0], case[2][1], C.byref(src.c), case[3][0], case[3][1], fx, fy)
+        cases.append(case); wants.append(want)
+        sources.append(dev.DeviceFrame32.from_numpy(src.array, src.full.tuple(), src.current.tuple()))
+    failures = []
+
+    def worker(seed):
+        try:
+            rng = np.random.default_rng(seed)
+            dev.check(dev.lib().cv_set_device(0), "cv_set_device")          # the device is a per-thread choice, like CUDA's
+            stream = C.c_void_p()
+            dev.check(dev.lib().cv_stream_create(C.byref(stream)), "cv_stream_create")
+            for _ in range(3):
+                for i in rng.permutation(16):
+                    fx, fy, tp, sp, swin, tfull = cases[i]
+                    out = dev.DeviceFrame32(tfull)
+                    dev.check(dev.lib().cv_scale_bilinear_f32(C.byref(out.c), A.V2f(*tp), C.byref(sources[i].c), A.V2f(*sp), A.V2f(fx, fy), stream), "scale")
+                    got = out.download(stream)
+                    check_scaled(got, out.current.tuple(), wants[i], False, "thread %d case %d" % (seed, i))
+            dev.lib().cv_stream_destroy(stream)
+        except BaseException as e:          # noqa: BLE001 -- reported by the main thread
+            failures.append(repr(e))
+
+    threads = [threading.Thread(target=worker, args=(s,)) for s in range(4)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not failures, failures[:2]
+
+
 def test_scale_1080p_to_4k_and_back_properties(dev):
     """Full-size properties: a constant image stays constant in the interior under 2x enlargement (the triangle taps
     of every target pixel sum to one) and under 1/2 reduction (taps normalised, filter.c:69-75).  The reduction is run
