@@ -90,7 +90,9 @@ def run_case(gpu, full, specs, seeds=100):
     assert out.current.tuple() == want.current.tuple()
     x0, y0, x1, y1 = want.current.tuple()
     got = out.download()
-    assert np.array_equal(got[y0:y1 + 1, x0:x1 + 1], want.array[y0:y1 + 1, x0:x1 + 1]), "fused layer filters differ from the oracle"
+    ys, xs = slice(y0 - full[1], y1 - full[1] + 1), slice(x0 - full[0], x1 - full[0] + 1)       # array indices of the window
+    assert got[ys, xs].size == (y1 - y0 + 1) * (x1 - x0 + 1) * 4
+    assert np.array_equal(got[ys, xs], want.array[ys, xs]), "fused layer filters differ from the oracle"
     return launches, want, (hosts, evens)
 
 
@@ -247,3 +249,41 @@ def check_python_filter_graph(dev, monkeypatch, full, weave_fits):
         x0, y0, x1, y1 = x.current_window.flat()
         xs, ys = slice(x0 - full[0], x1 - full[0] + 1), slice(y0 - full[1], y1 - full[1] + 1)
         assert np.array_equal(np.asarray(x.data)[ys, xs].view(np.uint8), np.asarray(y.data)[ys, xs].view(np.uint8))
+
+
+def test_random_layer_filters(gpu):
+    """random stacks (1-6 layers, random windows with even and odd edges, some outside the frame) with random filter
+    combinations per layer; fused launch against the oracle.  CV_OPS_FUZZ_CASES scales it (default 40)."""
+    import os
+    rng = np.random.default_rng(77)
+    for case in range(int(os.environ.get("CV_OPS_FUZZ_CASES", "40"))):
+        w, h = int(rng.choice([66, 130, 200, 257, 384])), int(rng.integers(4, 40))
+        ox, oy = int(rng.choice([0, 0, -6, 3, 10])), int(rng.integers(-3, 4))
+        full = (ox, oy, ox + w - 1, oy + h - 1)
+
+        def box():
+            if rng.random() < 0.3:
+                return full
+            a = int(rng.integers(ox - 4, ox + w - 1)); b = int(rng.integers(a, ox + w + 4))
+            c = int(rng.integers(oy - 2, oy + h)); d = int(rng.integers(c, oy + h + 2))
+            return (a, c, b, d)
+
+        specs = []
+        for _ in range(int(rng.integers(1, 7))):
+            clip = lambda b: (max(b[0], full[0]), max(b[1], full[1]), min(b[2], full[2]), min(b[3], full[3]))
+            window = clip(box())                # these frames share the output's full_window
+            if window[2] < window[0] or window[3] < window[1]:
+                window = full
+            ops = {}
+            if rng.random() < 0.3:              # the frame that supplies the even rows defines at least the layer's window
+                ops["weave"] = True
+                ops["even_window"] = clip((window[0] - int(rng.integers(0, 5)), window[1] - int(rng.integers(0, 4)),
+                                           window[2] + int(rng.integers(0, 5)), window[3] + int(rng.integers(0, 4))))
+            if rng.random() < 0.35:
+                ops["color"] = int(rng.choice([COLOR_TO_XYZ, COLOR_TO_SRGB]))
+            if rng.random() < 0.5:
+                ops["gain"], ops["offset"] = float(np.float32(rng.uniform(-0.5, 2.0))), float(np.float32(rng.uniform(-0.25, 0.25)))
+            if rng.random() < 0.35:
+                ops["crop"] = box()
+            specs.append((window, ops or None))
+        run_case(gpu, full, specs, seeds=2000 + 20 * case)
