@@ -215,3 +215,34 @@ def test_copy_frame_f16(dev):
     dev.check(dev.lib().cv_copy_frame_f16(C.byref(out.c), C.byref(dsrc.c), None))
     dev.sync()
     assert_frames_equal(out.download(), out.current.tuple(), want, "copy_frame_f16")
+
+
+def test_encode_u8_and_argb32_at_1080p(dev):
+    """frames large enough that every thread of k_encode_u8 / k_to_argb32 walks several pixels per iteration (the
+    four-pixel unroll and its tail), with an inset window: 8-bit outputs and the written-back frame bit for bit"""
+    full = (0, 0, 1919, 1079)
+    current = (3, 2, 1900, 1071)
+    frame = O.synth_frame(full, 79, current)
+    srgb = np.zeros(65536, np.uint16)
+    ramp = np.zeros(65536, np.uint8)
+    O.oracle().orc_build_lut(O.LUT_LINEAR_TO_SRGB, O.ptr(srgb))
+    O.oracle().orc_build_intent_ramp(1.25, O.ptr(ramp))
+    for write_back in (0, 1):
+        want_frame = frame.copy()
+        want_u8 = np.full((1080, 1920, 4), 0x5A, np.uint8)
+        O.oracle().orc_encode_u8(C.byref(want_frame.c), O.ptr(srgb), O.ptr(ramp), O.ptr(want_u8))
+        dframe = to_device(dev, frame)
+        target = dev.DeviceBuffer.from_numpy(np.full((1080, 1920, 4), 0x5A, np.uint8))
+        dev.check(dev.lib().cv_encode_u8(C.byref(dframe.c), dev.display_table(1.25), target.ptr, write_back, None))
+        assert np.array_equal(target.download(np.uint8, (1080, 1920, 4)), want_u8)
+        assert np.array_equal(dframe.download(), want_frame.array if write_back else frame.array)
+
+    ramp45 = np.zeros(65536, np.uint8)
+    O.oracle().orc_build_gamma45(O.ptr(ramp45))
+    rows, cols = current[3] - current[1] + 1, current[2] - current[0] + 1
+    want = np.zeros((rows, cols), np.uint32)
+    O.oracle().orc_to_argb32(C.byref(frame.c), O.ptr(ramp45), O.ptr(want))
+    dframe = to_device(dev, frame)
+    out = dev.DeviceBuffer(want.nbytes)
+    dev.check(dev.lib().cv_to_argb32(C.byref(dframe.c), out.ptr, None))
+    assert np.array_equal(out.download(np.uint32, want.shape), want)
