@@ -33,9 +33,13 @@ struct RectArgs {
 #ifndef CV_RECT_MAX_THREADS
 #define CV_RECT_MAX_THREADS 384       /* 168 registers: two units and the 4:2:2 groups of two rows stay in registers (512 threads spilled them) */
 #endif
+/* The instantiations with fused layer filters are bounded for 512 threads instead (128 registers, 16 to 96 bytes of
+ * spills): measured on the same box, 4K 4 layers with filters 7 620 -> 8 190 fps, while the plain ones lose at 512
+ * (1080p 4 layers 90.7 k -> 63.0 k at three pairs per lane, 90.1 k at two; the 4K timeline 11.8 k -> 10.7 k). */
+#define CV_RECT_OPS_MAX_THREADS 512
 
 template<int SHAPE, int PPL, bool OPS>
-__global__ void __launch_bounds__( CV_RECT_MAX_THREADS, 1 )
+__global__ void __launch_bounds__( OPS ? CV_RECT_OPS_MAX_THREADS : CV_RECT_MAX_THREADS, 1 )
 k_rect( const __grid_constant__ DevJob J0, const DevJob *__restrict__ jobs, const __grid_constant__ RectPlan plan,
         const RectPiece *__restrict__ pieces, const __grid_constant__ RectArgs A,
         const uint16_t *__restrict__ table /* staged: the compact conversion table */, const uint16_t *__restrict__ full_table ) {
@@ -437,10 +441,11 @@ static int launch_rect_ppl( CvDevice *dev, const DevJob *job, const DevJob *dev_
     A.all_units = plan->units_per_frame * (uint32_t) count;
 
     const size_t tables = (size_t) A.lut_bytes + A.u8_bytes;
-    static int max_warps = 0, small_warps = 0;
+    static int max_warps = 0, small_warps = 0;          /* per instantiation */
     if( !max_warps ) {
-        max_warps = env_int( "CV_RECT_WARPS", CV_RECT_MAX_THREADS / 32 );
-        if( max_warps < 1 || max_warps > CV_RECT_MAX_THREADS / 32 ) max_warps = CV_RECT_MAX_THREADS / 32;
+        constexpr int most = ( OPS ? CV_RECT_OPS_MAX_THREADS : CV_RECT_MAX_THREADS ) / 32;
+        max_warps = env_int( "CV_RECT_WARPS", most );
+        if( max_warps < 1 || max_warps > most ) max_warps = most;
         small_warps = env_int( "CV_RECT_SMALL_WARPS", 4 );
         if( small_warps < 1 || small_warps > max_warps ) small_warps = max_warps < 4 ? max_warps : 4;
     }
