@@ -448,3 +448,50 @@ def test_uniform_batch_matches_oracle(dev, shape):
         assert_frames_equal(outs[i].download(), outs[i].current.tuple(), wants[i], "%s batch job %d" % (shape, i))
         if u8s[i] is not None:
             assert np.array_equal(u8s[i].download(np.uint8, (h, w, 4)), want_u8[i]), "%s batch job %d: 8-bit output" % (shape, i)
+
+
+def test_large_mixed_batch_in_chunks(dev):
+    """cv_render_frames builds and launches a call in chunks of 1024 jobs; inside a chunk jobs are grouped by kind.
+    2 600 jobs of three kinds interleaved (a 4:2:2 conversion, a two-layer stack with a partial window, a crossfade),
+    each with its own output: every output against the oracle; then a bad job late in the batch makes the call fail."""
+    from canvas_b200 import _abi as A
+    full = (0, 0, 63, 7)
+    orc = O.oracle()
+    pic = O.synth_coded(64, 8, 5, 2, O.LAYOUT_UYVY, O.MATRIX_709, (0, 0))
+    dpic = device_coded(dev, pic)
+    la, lb = O.synth_frame(full, 11, full), O.synth_frame(full, 12, (6, 1, 50, 6))
+    dla, dlb = to_device(dev, la), to_device(dev, lb)
+
+    want_convert = O.HostFrame16(full)
+    orc.orc_reconstruct(C.byref(want_convert.c), C.byref(pic.c))
+    want_stack = O.HostFrame16(full)
+    orc.orc_composite_f16(C.byref(want_stack.c), (O.Frame16 * 2)(la.c, lb.c), 2)
+    want_cross = O.HostFrame16(full)
+    orc.orc_cross_f16(C.byref(want_cross.c), C.byref(la.c), C.byref(lb.c), 0.375)
+    wants = [want_convert, want_stack, want_cross]
+
+    count = 2600
+    outs = [dev.DeviceFrame16(full) for _ in range(count)]
+    jobs = []
+    for i, out in enumerate(outs):
+        kind = (i * 7 + i // 5) % 3
+        if kind == 0:
+            jobs.append(dev.make_job(out=out, a=dpic))
+        elif kind == 1:
+            jobs.append(dev.make_job(out=out, layers=[dla, dlb]))
+        else:
+            jobs.append(dev.make_job(out=out, a=dla, b=dlb, mix_b=0.375))
+    dev.render_frames(jobs)
+    dev.sync()
+    for i in range(0, count, 37):           # a spread of them (downloading all 2 600 would only cost time)
+        kind = (i * 7 + i // 5) % 3
+        assert_frames_equal(outs[i].download(), outs[i].current.tuple(), wants[kind], "job %d kind %d" % (i, kind))
+    for i in (1023, 1024, 1025, 2047, 2048, 2599):
+        kind = (i * 7 + i // 5) % 3
+        assert_frames_equal(outs[i].download(), outs[i].current.tuple(), wants[kind], "job %d kind %d" % (i, kind))
+
+    bad = dev.make_job(out=outs[0], a=dpic)
+    bad.layer_count = 99
+    arr = (dev.FrameJob * 1500)(*(jobs[:1400] + [bad] + jobs[1401:1500]))
+    assert dev.lib().cv_render_frames(arr, 1500, None) != 0
+    dev.sync()
