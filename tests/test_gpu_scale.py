@@ -290,3 +290,39 @@ def test_gain_offset_arithmetic(dev):
     want = data.copy()
     want[..., :3] = want[..., :3] * np.float32(gain) + np.float32(offset)       # mul, then add: two roundings
     assert np.array_equal(got.data[2:30, 3:61].view(np.uint32), want[2:30, 3:61].view(np.uint32))
+
+
+def test_scaler_on_a_second_gpu(dev):
+    """the tap-table cache and the static scratch are per device: the same geometry on GPU 1 after GPU 0, both entry
+    points, against the oracle (skipped on a one-GPU box)"""
+    import threading
+    from canvas_b200 import _abi as A
+    lib = dev.lib()
+    if lib.cv_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    case = (1.5, 1.25, (2.0, 1.0), (0.5, 3.5), (3, 1, 200, 120), (-2, -3, 320, 170))
+    fx, fy, tp, sp, swin, tfull = case
+    src = source_frame(case, seed=99)
+    want = O.HostFrame32(tfull)
+    O.oracle().orc_scale_bilinear_f32(C.byref(want.c), tp[0], tp[1], C.byref(src.c), sp[0], sp[1], fx, fy)
+    failures = []
+
+    def on_device(index):
+        try:
+            dev.check(lib.cv_init(index), "cv_init")            # selects the device for this thread
+            dsrc = dev.DeviceFrame32.from_numpy(src.array, src.full.tuple(), src.current.tuple())
+            for entry in ("cv_scale_bilinear_f32", "cv_scale_bilinear_static_f32", "cv_scale_bilinear_f32"):
+                out = dev.DeviceFrame32(tfull)
+                dev.check(getattr(lib, entry)(C.byref(out.c), A.V2f(*tp), C.byref(dsrc.c), A.V2f(*sp), A.V2f(fx, fy), None), entry)
+                dev.sync()
+                check_scaled(out.download(), out.current.tuple(), want, False, "%s on GPU %d" % (entry, index))
+                out.free()
+            dsrc.free()
+        except BaseException as e:          # noqa: BLE001
+            failures.append("GPU %d: %r" % (index, e))
+
+    for index in (0, 1, 0):
+        t = threading.Thread(target=on_device, args=(index,))
+        t.start()
+        t.join()
+    assert not failures, failures
