@@ -312,8 +312,7 @@ k_rect( const __grid_constant__ DevJob J0, const DevJob *__restrict__ jobs, cons
                     for( int q = 0; q < PPL; q++ ) {
                         const uint4 raw = lds_u4( slot + q * 512 );
                         const int x = cur.x0 + 2 * ( q * 32 + lane );
-                        b[q] = join_pair( layer_ops_px( J0, J0.layer[k], make_uint2( raw.x, raw.y ), x, y ),
-                                          layer_ops_px( J0, J0.layer[k], make_uint2( raw.z, raw.w ), x + 1, y ) );
+                        b[q] = layer_ops_pair( J0, J0.layer[k], raw, x, y );
                     }
                 }
                 else {
