@@ -721,6 +721,7 @@ static int color_transform( rgba_frame_f16 *frame, const float m[9], int pre, in
     A.pre = pre >= 0 ? (const uint16_t *) dev->lut[pre] : NULL;
     A.post = post >= 0 ? (const uint16_t *) dev->lut[post] : NULL;
     memcpy( A.m, m, sizeof(A.m) );
+    A.one = 1.0f;
     return cvi_launch_color( &A, cvi_stream( stream ) );
 }
 

@@ -138,6 +138,7 @@ typedef struct ColorArgs {
     uint2 *frame; int32_t pitch, ox, oy; DevBox win; uint32_t width, total, magic;
     const uint16_t *pre, *post;                             /* tables applied to all four channels before / after, or NULL */
     float m[9];                                             /* out.x = (r*m[0] + g*m[1]) + b*m[2], ... */
+    float one;                                              /* 1.0f, opaque to the compiler (see add2_unfused in cv_device.cuh) */
 } ColorArgs;
 
 typedef struct Mpeg2Args {
