@@ -246,3 +246,27 @@ def test_encode_u8_and_argb32_at_1080p(dev):
     out = dev.DeviceBuffer(want.nbytes)
     dev.check(dev.lib().cv_to_argb32(C.byref(dframe.c), out.ptr, None))
     assert np.array_equal(out.download(np.uint32, want.shape), want)
+
+
+def test_half_from_float_at_every_truncation_boundary(dev):
+    """every half value as a float, the float just above it and the float just below the next half, both signs, finite
+    halves only (so that whole quads take the hardware-conversion path of k_half_from_float), plus the same mixed with
+    values that force the bit-exact integer path: truncation, subnormals and the boundaries bit for bit"""
+    halves = np.arange(0x7C00, dtype=np.uint16)                      # finite, positive
+    exact = np.zeros(halves.size, np.float32)
+    O.oracle().orc_h2f_n(O.ptr(exact), O.ptr(halves), halves.size)
+    bits = exact.view(np.uint32)
+    nxt = np.concatenate([bits[1:], np.array([0x47800000], np.uint32)])           # the next half as a float (65536 after the last)
+    patterns = np.concatenate([bits, bits + 1, nxt - 1])
+    patterns = np.concatenate([patterns, patterns | 0x80000000]).astype(np.uint32)
+    mixed = patterns.copy()
+    mixed[::7] = 0x7FC01234                                          # a NaN with a payload in every second quad or so
+    mixed[3::11] = 0x4B000000
+    for values in (patterns, mixed):
+        floats = values.view(np.float32)
+        want = np.zeros(floats.shape, np.uint16)
+        O.oracle().orc_f2h_n(O.ptr(want), O.ptr(floats), floats.size)
+        src = dev.DeviceBuffer.from_numpy(floats)
+        dst = dev.DeviceBuffer(2 * floats.size)
+        dev.check(dev.lib().cv_half_from_float(dst.ptr, src.ptr, floats.size, None))
+        assert np.array_equal(dst.download(np.uint16, floats.shape), want)
