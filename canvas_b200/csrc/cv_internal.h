@@ -117,7 +117,7 @@ typedef struct ScaleArgs {
 /* both passes in one launch (cv_scale_fused.cu): a block = a TX x TY tile of the target, its slice of the temporary in
  * shared memory.  Pass 1 fills the temporary (lines1 lines starting at coordinate origin1 along its axis, cross range
  * cross1 on the other), pass 2 reads it. */
-enum { CV_SCALE_FUSED_TX = 64, CV_SCALE_FUSED_TY = 16,
+enum { CV_SCALE_FUSED_TX = 64, CV_SCALE_FUSED_TY = 16, CV_SCALE_FUSED_TY_SHORT = 8,      /* tile rows: enlargements / the rest */
        CV_SCALE_FUSED_MAX_TEMP = 3072,      /* pixels of the temporary per tile: 48 KB of shared memory (measured: with 96 KB a
                                              * 3:1 reduction fits but runs at 0.029 ms against 0.023 ms for the two passes) */
        CV_SCALE_FUSED_MAX_TAPS = 1024 };    /* taps of one pass that a tile's lines may have (staged in shared memory) */
@@ -132,6 +132,7 @@ typedef struct FusedScaleArgs {
     uint32_t temp_pixels;                                /* largest slice of the temporary any tile needs */
     float one;                                           /* 1.0f, opaque to the compiler (see tap_accumulate) */
     uint32_t cap1, cap2;                                 /* most taps of a pass that any tile's lines have, rounded up to 4 */
+    int32_t tile_rows;                                   /* CV_SCALE_FUSED_TY or CV_SCALE_FUSED_TY_SHORT */
 } FusedScaleArgs;
 
 typedef struct ColorArgs {

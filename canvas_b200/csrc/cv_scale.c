@@ -368,12 +368,16 @@ static int fused_build( ScaleEntry *e, const box2i *s, const box2i *t, v2f targe
 
     const int lines1 = vertical1 ? want->max.y - want->min.y + 1 : want->max.x - want->min.x + 1;
     const int lines2 = vertical2 ? th : tw;
-    const int slice = widest_slice( &plan2, lines2, vertical2 ? CV_SCALE_FUSED_TY : CV_SCALE_FUSED_TX );
-    const long long temp_pixels = (long long) slice * ( vertical2 ? CV_SCALE_FUSED_TX : CV_SCALE_FUSED_TY );
+    /* tile height: 16 rows when both axes enlarge (1080p -> 4K: 0.050 ms against 0.060 ms with 8), 8 rows otherwise
+     * (4K -> 1080p 0.021 against 0.025 ms; a 3:1 reduction fits only with 8 and then beats the two passes, 0.019 against
+     * 0.023 ms) */
+    const int tile_rows = ( factors.x > 1.0f && factors.y > 1.0f ) ? CV_SCALE_FUSED_TY : CV_SCALE_FUSED_TY_SHORT;
+    const int slice = widest_slice( &plan2, lines2, vertical2 ? tile_rows : CV_SCALE_FUSED_TX );
+    const long long temp_pixels = (long long) slice * ( vertical2 ? CV_SCALE_FUSED_TX : tile_rows );
     /* pass 1 is indexed by the tile's lines along the OTHER axis (rows of the tile for a vertical first pass) */
-    const int taps1 = vertical1 ? most_taps( &plan1, lines1, t->min.y - want->min.y, th, CV_SCALE_FUSED_TY )
+    const int taps1 = vertical1 ? most_taps( &plan1, lines1, t->min.y - want->min.y, th, tile_rows )
                                 : most_taps( &plan1, lines1, t->min.x - want->min.x, tw, CV_SCALE_FUSED_TX );
-    const int taps2 = most_taps( &plan2, lines2, 0, lines2, vertical2 ? CV_SCALE_FUSED_TY : CV_SCALE_FUSED_TX );
+    const int taps2 = most_taps( &plan2, lines2, 0, lines2, vertical2 ? tile_rows : CV_SCALE_FUSED_TX );
     if( slice < 0 || temp_pixels > CV_SCALE_FUSED_MAX_TEMP || taps1 > CV_SCALE_FUSED_MAX_TAPS || taps2 > CV_SCALE_FUSED_MAX_TAPS ) {
         plan_free( &plan1 ); plan_free( &plan2 );
         return 0;
@@ -413,6 +417,7 @@ static int fused_build( ScaleEntry *e, const box2i *s, const box2i *t, v2f targe
         A->coef2 = (const float *) d;
         A->temp_pixels = (uint32_t)( temp_pixels > 0 ? temp_pixels : 1 );
         A->one = 1.0f;
+        A->tile_rows = tile_rows;
         A->cap1 = (uint32_t)( ( taps1 + 3 ) & ~3 ); A->cap2 = (uint32_t)( ( taps2 + 3 ) & ~3 );
         window_after( &e->window, &plan2, vertical2, cross2_lo, cross2_hi );
     }

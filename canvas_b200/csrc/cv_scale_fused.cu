@@ -3,7 +3,8 @@
  *
  * /root/reference/src/cprocess/video_scale.c:247-284 resamples the axis with the smaller factor into a temporary
  * frame and the other axis from that temporary.  As two launches (k_scale_axis, cv_kernels.cu) the temporary costs
- * a write and a read of HBM that the algorithm does not need.  Here a block produces a TX x TY tile of the target:
+ * a write and a read of HBM that the algorithm does not need.  Here a block produces a TX x TY tile of the target (TY = 16
+ * rows for enlargements, whose slices of the temporary are small, 8 otherwise -- measured per geometry, cv_scale.c):
  *   1. the tile's slices of both tap tables go to shared memory (two rounds of independent loads instead of a
  *      chain of dependent ones per pixel),
  *   2. exactly the pixels of the temporary that the tile's second-pass taps touch are evaluated into shared memory --
@@ -50,10 +51,10 @@ __device__ __forceinline__ Acc acc_zero() { Acc a; a.lo = make_float2( 0.0f, 0.0
 
 /* first pass = vertical (X_FIRST == 0): temporary( xs, yt ) over source columns and target rows
  * first pass = horizontal (X_FIRST == 1): temporary( xt, ys ) over target columns and source rows */
-template<int X_FIRST>
+template<int X_FIRST, int TY>
 __global__ void __launch_bounds__( FUSED_THREADS, 8 ) k_scale_fused( const __grid_constant__ FusedScaleArgs A ) {
     extern __shared__ float4 temp[];
-    constexpr int TX = CV_SCALE_FUSED_TX, TY = CV_SCALE_FUSED_TY, ROWS = TY / ( FUSED_THREADS / TX );
+    constexpr int TX = CV_SCALE_FUSED_TX, ROWS = TY / ( FUSED_THREADS / TX );
     const FusedTables T( temp + A.temp_pixels, A.cap1, A.cap2 );
 
     const int c0 = (int) blockIdx.x * TX, r0 = (int) blockIdx.y * TY;
@@ -184,23 +185,32 @@ extern "C" int cvi_launch_scale_fused( const FusedScaleArgs *args, cudaStream_t 
     if( !dev ) return CV_ERR_NOT_INITIALISED;
     if( !args->t_width || !args->t_height ) return CV_OK;
     static_assert( CV_SCALE_FUSED_TX >= CV_SCALE_FUSED_TY && CV_SCALE_FUSED_TX + 1 <= 128 && FUSED_THREADS % CV_SCALE_FUSED_TX == 0
-                   && CV_SCALE_FUSED_TY % ( FUSED_THREADS / CV_SCALE_FUSED_TX ) == 0, "tile shape" );
-    if( args->temp_pixels > CV_SCALE_FUSED_MAX_TEMP || args->cap1 > CV_SCALE_FUSED_MAX_TAPS || args->cap2 > CV_SCALE_FUSED_MAX_TAPS || ( args->cap1 | args->cap2 ) % 4 )
-        return cvi_fail( CV_ERR_ARGUMENT, "k_scale_fused: %u pixels of the temporary per tile (at most %u)", args->temp_pixels, (unsigned) CV_SCALE_FUSED_MAX_TEMP );
+                   && CV_SCALE_FUSED_TY % ( FUSED_THREADS / CV_SCALE_FUSED_TX ) == 0 && CV_SCALE_FUSED_TY_SHORT % ( FUSED_THREADS / CV_SCALE_FUSED_TX ) == 0, "tile shape" );
+    if( args->temp_pixels > CV_SCALE_FUSED_MAX_TEMP || args->cap1 > CV_SCALE_FUSED_MAX_TAPS || args->cap2 > CV_SCALE_FUSED_MAX_TAPS || ( args->cap1 | args->cap2 ) % 4
+            || ( args->tile_rows != CV_SCALE_FUSED_TY && args->tile_rows != CV_SCALE_FUSED_TY_SHORT ) )
+        return cvi_fail( CV_ERR_ARGUMENT, "k_scale_fused: %u pixels of the temporary per tile (at most %u), %d rows", args->temp_pixels, (unsigned) CV_SCALE_FUSED_MAX_TEMP, args->tile_rows );
 
     static int configured[CV_MAX_DEVICES];          /* more than 48 KB of dynamic shared memory is opt-in, per device */
     const size_t most = (size_t) CV_SCALE_FUSED_MAX_TEMP * sizeof(float4) + fused_table_bytes( CV_SCALE_FUSED_MAX_TAPS, CV_SCALE_FUSED_MAX_TAPS );
     if( !configured[dev->index] ) {
-        int rc = cvi_cuda( cudaFuncSetAttribute( k_scale_fused<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) most ), "cudaFuncSetAttribute(k_scale_fused)" );
-        if( !rc ) rc = cvi_cuda( cudaFuncSetAttribute( k_scale_fused<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) most ), "cudaFuncSetAttribute(k_scale_fused)" );
+        int rc = cvi_cuda( cudaFuncSetAttribute( k_scale_fused<0, CV_SCALE_FUSED_TY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) most ), "cudaFuncSetAttribute(k_scale_fused)" );
+        if( !rc ) rc = cvi_cuda( cudaFuncSetAttribute( k_scale_fused<1, CV_SCALE_FUSED_TY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) most ), "cudaFuncSetAttribute(k_scale_fused)" );
+        if( !rc ) rc = cvi_cuda( cudaFuncSetAttribute( k_scale_fused<0, CV_SCALE_FUSED_TY_SHORT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) most ), "cudaFuncSetAttribute(k_scale_fused)" );
+        if( !rc ) rc = cvi_cuda( cudaFuncSetAttribute( k_scale_fused<1, CV_SCALE_FUSED_TY_SHORT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) most ), "cudaFuncSetAttribute(k_scale_fused)" );
         if( rc ) return rc;
         configured[dev->index] = 1;
     }
 
-    const dim3 grid( ( args->t_width + CV_SCALE_FUSED_TX - 1 ) / CV_SCALE_FUSED_TX, ( args->t_height + CV_SCALE_FUSED_TY - 1 ) / CV_SCALE_FUSED_TY );
+    const dim3 grid( ( args->t_width + CV_SCALE_FUSED_TX - 1 ) / CV_SCALE_FUSED_TX, ( args->t_height + args->tile_rows - 1 ) / args->tile_rows );
     const size_t shared = (size_t) args->temp_pixels * sizeof(float4) + fused_table_bytes( args->cap1, args->cap2 );
-    if( args->x_first ) k_scale_fused<1><<<grid, FUSED_THREADS, shared, stream>>>( *args );
-    else k_scale_fused<0><<<grid, FUSED_THREADS, shared, stream>>>( *args );
+    if( args->tile_rows == CV_SCALE_FUSED_TY ) {
+        if( args->x_first ) k_scale_fused<1, CV_SCALE_FUSED_TY><<<grid, FUSED_THREADS, shared, stream>>>( *args );
+        else k_scale_fused<0, CV_SCALE_FUSED_TY><<<grid, FUSED_THREADS, shared, stream>>>( *args );
+    }
+    else {
+        if( args->x_first ) k_scale_fused<1, CV_SCALE_FUSED_TY_SHORT><<<grid, FUSED_THREADS, shared, stream>>>( *args );
+        else k_scale_fused<0, CV_SCALE_FUSED_TY_SHORT><<<grid, FUSED_THREADS, shared, stream>>>( *args );
+    }
     cvi_count_launch( 1 );
     return cvi_cuda( cudaGetLastError(), "k_scale_fused launch" );
 }
