@@ -118,8 +118,9 @@ typedef struct ScaleArgs {
  * shared memory.  Pass 1 fills the temporary (lines1 lines starting at coordinate origin1 along its axis, cross range
  * cross1 on the other), pass 2 reads it. */
 enum { CV_SCALE_FUSED_TX = 64, CV_SCALE_FUSED_TY = 16, CV_SCALE_FUSED_TY_SHORT = 8,      /* tile rows: enlargements / the rest */
-       CV_SCALE_FUSED_MAX_TEMP = 3072,      /* pixels of the temporary per tile: 48 KB of shared memory (measured: with 96 KB a
-                                             * 3:1 reduction fits but runs at 0.029 ms against 0.023 ms for the two passes) */
+       CV_SCALE_FUSED_MAX_TEMP = 3072,      /* pixels of the temporary per tile: 48 KB of shared memory (measured: with 96 KB and
+                                             * 16-row tiles a 3:1 reduction runs at 0.029 ms against 0.023 ms for the two passes;
+                                             * with 8-row tiles it fits 48 KB and runs at 0.019 ms) */
        CV_SCALE_FUSED_MAX_TAPS = 1024 };    /* taps of one pass that a tile's lines may have (staged in shared memory) */
 typedef struct FusedScaleArgs {
     float4 *target; int32_t t_pitch, t_ox, t_oy; uint32_t t_width, t_height;
